@@ -1,0 +1,86 @@
+// Device-side data layout of the render core (sm_100a).
+//
+//  * BVH: only INTERNAL nodes are stored, one 64-byte record (4 x float4, 64-byte aligned) per node holding BOTH
+//    children's boxes and both child references, so one visit = one cache-line-half fetch instead of the
+//    reference's node + two child loads (scene.cu:145-201). Valid because children are always adjacent.
+//      q0 = {c0.min.x, c0.min.y, c0.min.z, c0.max.x}
+//      q1 = {c0.max.y, c0.max.z, c1.min.x, c1.min.y}
+//      q2 = {c1.min.z, c1.max.x, c1.max.y, c1.max.z}
+//      q3 = {ref0, ref1, 0, 0} (as ints)
+//    ref: bit31 clear -> index of an internal record; bit31 set -> leaf: bits[30:27] = triangle count (1..15),
+//    bits[26:0] = first triangle. Larger leaves (no_bvh, SAH refusals) are split into chains of same-box records
+//    by the packer. An absent child has an inverted box (never hit) and ref = kEmptyRef.
+//  * Triangles: 3 x float4 = {p1 | n.x}, {e1 | n.y}, {e2 | n.z} (precomputed-edge form, scene.cuh:15-33), BVH order.
+//  * Materials: 3 x float4, the reference's 48-byte record. Spheres: float4. Environment map: float4 texels.
+//  * Ray queues: SoA, 40 bytes per live ray:
+//      qa = {o.x, o.y, o.z, d.x}   qb = {d.y, d.z, T.r, T.g}   qc = {T.b, ray id (bits)}
+//    Radiance is not carried: it is added to the framebuffer when it is found (miss / emissive hit).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rtd {
+
+constexpr uint32_t kLeafBit = 0x80000000u;
+constexpr uint32_t kEmptyRef = 0xFFFFFFFFu;  // leaf bit set, count 15, start 0x7FFFFFF: never reached (box is inverted)
+constexpr int kLeafCountShift = 27;
+constexpr uint32_t kLeafStartMask = (1u << kLeafCountShift) - 1u;
+constexpr int kMaxLeafTris = 15;
+constexpr int kStackDepth = 32;  // per-thread traversal stack entries in shared memory
+
+// accept t iff t > kTMin: the reference rejects `t < 0.005` in DOUBLE (scene.cu:190,357,366); 0.005f is the largest
+// float below 0.005, so for float t:  (double)t < 0.005  <=>  t <= 0.005f.
+constexpr float kTMin = 0.005f;
+constexpr float kMissT = 1e30f;
+
+struct DeviceScene {
+    const float4 *nodes;      // 4 per internal record
+    const float4 *tris;       // 3 per triangle
+    const float4 *materials;  // 3 per material
+    const float4 *spheres;
+    const float4 *env;
+    const uint16_t *material_indices;
+    int32_t sphere_count, tri_count, env_w, env_h;
+    int32_t width, height;
+    float cam[3], top_left[3], right[3], up[3];
+    float inv_width, inv_height;
+    float min_coord[3], inv_dim[3];
+};
+
+struct RayQueue {
+    float4 *qa;
+    float4 *qb;
+    float2 *qc;
+};
+
+// Per-pass device counters (zeroed by one memset per pass).
+struct PassCounters {
+    uint32_t cursor[33];  // work-fetch cursor of bounce b
+    uint32_t count[33];   // live rays entering bounce b (count[0] unused: known on the host)
+};
+
+struct RenderTotals {
+    unsigned long long live_ray_bounces;
+    unsigned long long internal_visits;
+    unsigned long long triangle_tests;
+    unsigned long long live_per_bounce[32];
+};
+
+struct BounceArgs {
+    RayQueue in, out;
+    const uint32_t *order;  // optional permutation of the input queue (reorder pass), else nullptr
+    uint32_t *keys_out;     // optional: reorder key of every ray written to `out`
+    PassCounters *pc;
+    RenderTotals *totals;
+    float *framebuffer;     // 3 floats per pixel, un-normalised sums
+    uint32_t n_first;       // rays in the pass (bounce 0 only)
+    int32_t bounce;
+    int32_t rays_per_pixel; // of this pass
+    uint32_t gen_seed;      // 709579 * remaining_rays          (scene.cu:81)
+    uint32_t proc_seed;     // 279220567 * (remaining*20+bounce) (raytracing.cu:89,236)
+    unsigned long long pcg_inc;  // 820957824423429 | 1 for stream 0 (random.cuh:28)
+    int32_t key_bits;
+};
+
+}  // namespace rtd

@@ -1,0 +1,146 @@
+/* include/rt_core.h — C ABI of the B200-native render core (librtcore.so).
+ *
+ * This is the drop-in boundary for the reference's GPU render path. The reference has no FFI layer;
+ * its de-facto operator boundary is
+ *
+ *     Vec3 *gpu_raytrace(const Scene *scene, bool sort)      /root/reference/raytracing.cu:170-284
+ *
+ * followed by the inline bloom block of main()               /root/reference/raytracing.cu:360-392
+ * and the host tone map                                       /root/reference/raytracing.cu:286-303.
+ *
+ * Everything here is `extern "C"`, plain pointers and sizes. Caller owns every host buffer; the
+ * library owns all device memory (freed by rt_destroy). Functions return RT_OK (0) or a negative
+ * rt_status and never call exit(); rt_last_error() gives the message. One rt_ctx is bound to one
+ * CUDA device and must be used by one host thread at a time. There is NO CPU fallback: without a
+ * usable CUDA device rt_create fails with RT_ERR_NO_DEVICE.
+ *
+ * Array layouts are the reference's own (scene.cuh), so a maintainer can pass the fields of a
+ * loaded `Scene` straight through (INTEGRATION.md shows the stub).
+ */
+#ifndef RT_CORE_H
+#define RT_CORE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RT_API_VERSION 1
+
+typedef enum rt_status {
+    RT_OK = 0,
+    RT_ERR_INVALID = -1,   /* bad argument / scene not uploaded */
+    RT_ERR_NO_DEVICE = -2, /* no CUDA device, or device index out of range */
+    RT_ERR_CUDA = -3,      /* a CUDA runtime call or kernel failed (message in rt_last_error) */
+    RT_ERR_NOMEM = -4,
+    RT_ERR_IO = -5,        /* host scene layer: file missing / malformed */
+    RT_ERR_PARSE = -6      /* host scene layer: e.g. material used before definition */
+} rt_status;
+
+/* Replaces the `Scene` POD the reference hands to gpu_raytrace (scene.cuh:102-166). */
+typedef struct rt_scene_desc {
+    const float *spheres;              /* sphere_count x {cx, cy, cz, radius}            scene.cuh:9-13   */
+    int32_t sphere_count;
+    const float *triangles;            /* triangle_count x {p1, p2-p1, p3-p1, normal}    scene.cuh:27-33, render form, BVH order */
+    int32_t triangle_count;
+    const uint16_t *material_indices;  /* sphere_count + triangle_count entries          scene.cuh:114    */
+    const float *materials;            /* material_count x {diffuse[3], metallicity, specular[3], roughness, emitted[3], ior}  scene.cuh:42-59 */
+    int32_t material_count;
+    const void *bvh_nodes;             /* bvh_node_count x 32 B {min[3], max[3], int child1, int child2}  scene.cuh:82-100 */
+    int32_t bvh_node_count;
+    const float *environment_map;      /* env_width*env_height x rgb                     scene.cuh:132    */
+    int32_t env_width, env_height;
+    int32_t width, height;             /* output image                                   scene.cuh:129-130 */
+    int32_t ray_count;                 /* rays (samples) per pixel                       scene.cuh:157    */
+    int32_t bounces;                   /*                                                scene.cuh:156    */
+    float exposure;                    /*                                                scene.cuh:139    */
+    float camera_position[3];          /*                                                scene.cuh:134    */
+    float near_plane_top_left[3];      /* precompute_camera_data, scene.cu:62-76 */
+    float scaled_right[3];
+    float scaled_up[3];
+    float inv_width, inv_height;
+    float min_coord[3];                /* scene bounds for the reorder key               scene.cu:822-830 */
+    float inv_dimensions[3];
+} rt_scene_desc;
+
+typedef struct rt_render_opts {
+    int32_t sort;          /* 1 = reorder live rays between bounces (reference default), 0 = `no_sort` (raytracing.cu:320-323) */
+    int32_t pass_spp;      /* samples per pixel per pass; 0 = 20 = MAX_RAYS_PER_PIXEL_PER_PASS (raytracing.cu:109). Seeds are
+                              defined per pass, so changing it changes the random streams (not the statistics). */
+    int32_t pass_first;    /* render only passes [pass_first, pass_first+pass_count) of ceil(ray_count/pass_spp); */
+    int32_t pass_count;    /* pass_count <= 0 = all remaining. Used for the per-GPU spp split. */
+    int32_t collect_stats; /* 1 = count node visits / triangle tests (slower kernel variant) */
+    int32_t stream_id;     /* 0 = reference-compatible PCG streams (raytracing.cu:89,229,236 with slot == ray id);
+                              k > 0 = disjoint PCG streams: stream k's `inc` differs (random.cuh:28), for multi-GPU runs
+                              that do NOT want pass-identical images */
+    int32_t sort_bits;     /* key width for the reorder pass, 0 = default */
+    int32_t reserved;
+} rt_render_opts;
+
+typedef struct rt_stats {
+    double loop_seconds;        /* CUDA-event time of the pass loop on the context's stream */
+    double total_seconds;       /* host wall time of the call ("GPU Took" equivalent, raytracing.cu:172-281) */
+    int64_t primary_rays;
+    int64_t live_ray_bounces;   /* non-early-out process_ray equivalents (SURVEY §8d metric unit) */
+    int64_t internal_visits;    /* valid when collect_stats */
+    int64_t triangle_tests;     /* valid when collect_stats */
+    int64_t sorted_pairs;       /* (key,index) pairs pushed through the reorder pass */
+    int32_t kernel_launches;    /* kernels of THIS library launched inside the loop */
+    int32_t passes;
+    double trace_shade_ms;      /* CUDA-event sum over the bounce kernels (0 unless collect_stats or RT_TIMING=1) */
+    double sort_ms;
+    int64_t live_per_bounce[32];
+} rt_stats;
+
+typedef struct rt_ctx rt_ctx;
+
+int rt_api_version(void);
+int rt_device_count(void);
+/* device: CUDA ordinal (honours CUDA_VISIBLE_DEVICES). */
+int rt_create(rt_ctx **out, int device);
+void rt_destroy(rt_ctx *ctx);
+/* ctx may be NULL for errors of rt_create / the host scene layer (thread-local). */
+const char *rt_last_error(const rt_ctx *ctx);
+
+/* Replaces Scene::copy_from_cpu_async + the __constant__ symbol (scene.cu:243-265, raytracing.cu:19):
+ * packs the BVH into 64-byte two-child records and the triangles into 3 x float4, uploads all. */
+int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *scene);
+/* Change the image block without re-uploading geometry (width/height/ray_count/bounces/exposure + camera basis). */
+int rt_scene_set_image(rt_ctx *ctx, const rt_scene_desc *scene);
+
+/* Replaces gpu_raytrace (raytracing.cu:170-284): out_rgb_sum = 3*width*height floats, row-major, top row first,
+ * UN-NORMALISED radiance sums, caller-owned host memory (pageable or pinned). opts/stats may be NULL. */
+int rt_render(rt_ctx *ctx, const rt_render_opts *opts, float *out_rgb_sum, rt_stats *stats);
+/* Same, but the sums stay in the context's device framebuffer; *out_dev (may be NULL) receives the device pointer
+ * (valid until the next render / rt_destroy). Used when a collective (NCCL reduce) follows. The stream is synchronised. */
+int rt_render_device(rt_ctx *ctx, const rt_render_opts *opts, float **out_dev, rt_stats *stats);
+
+/* Replaces the bloom block (raytracing.cu:21-74,360-392) and write_framebuffer_to_output_image (:286-303), on device.
+ * Operates in place on the context's device framebuffer. Any output pointer may be NULL.
+ *   bloom != 0: high-pass at 0.7*ray_count, 11-tap H+V box blur, add.
+ *   out_rgb_sum: 3*W*H floats after bloom; out_rgb8: 3*W*H bytes, tone-mapped. */
+int rt_postprocess(rt_ctx *ctx, int bloom, float *out_rgb_sum, uint8_t *out_rgb8);
+/* Load sums into the device framebuffer (e.g. after a host-side combine); n = 3*W*H floats. */
+int rt_framebuffer_upload(rt_ctx *ctx, const float *rgb_sum);
+
+/* ---- kernel-level entry points (parity hooks; each runs the production device code) ---- */
+
+/* Closest hit of n rays {ox,oy,oz,dx,dy,dz}: Scene::bvh_closest_hit_distance (scene.cu:134-241), preceded by the
+ * sphere loop (scene.cu:338-372) when with_spheres != 0. Miss: prim = -1, t = 1e30. prim is the reference's primitive
+ * index (sphere_count + triangle index in BVH order). */
+int rt_trace_closest(rt_ctx *ctx, const float *rays6, int32_t n, int32_t with_spheres, int32_t *out_prim, float *out_t,
+                     rt_stats *stats);
+/* Scene::generate_initial_rays (scene.cu:78-105) for ray indices [first, first+n) of a pass: 12 floats per ray
+ * {origin, direction, transmitted, collected}. seed = remaining_rays of the pass. */
+int rt_generate_rays(rt_ctx *ctx, int32_t rays_per_pixel, int32_t first, int32_t n, int32_t seed, float *out_ray_data12);
+/* One Scene::process_ray step (scene.cu:320-487) per record, rng = xor_srand(seeds[i]) (random.cuh:25-30); in place. */
+int rt_process_rays(rt_ctx *ctx, float *ray_data12, const uint32_t *seeds, int32_t n);
+/* The reorder pass on its own: stable LSD radix sort of (key, value) pairs on the low `bits` bits. Replaces
+ * cub::DeviceRadixSort::SortPairs (raytracing.cu:194-195,240-246). In place on host arrays. */
+int rt_sort_pairs(rt_ctx *ctx, uint32_t *keys, uint32_t *values, int32_t n, int32_t bits);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RT_CORE_H */
