@@ -9,7 +9,8 @@
 //      q3 = {ref0, ref1, 0, 0} (as ints)
 //    ref: bit31 clear -> index of an internal record; bit31 set -> leaf: bits[30:27] = triangle count (1..15),
 //    bits[26:0] = first triangle. Larger leaves (no_bvh, SAH refusals) are split into chains of same-box records
-//    by the packer. An absent child has an inverted box (never hit) and ref = kEmptyRef.
+//    by the packer. An absent child has a far-away degenerate box (an inverted box would pass the
+//    order-agnostic slab test) and ref = kEmptyRef.
 //  * Triangles: 3 x float4 = {p1 | n.x}, {e1 | n.y}, {e2 | n.z} (precomputed-edge form, scene.cuh:15-33), BVH order.
 //  * Materials: 3 x float4, the reference's 48-byte record. Spheres: float4. Environment map: float4 texels.
 //  * Ray queues: SoA, 40 bytes per live ray:
@@ -23,7 +24,7 @@
 namespace rtd {
 
 constexpr uint32_t kLeafBit = 0x80000000u;
-constexpr uint32_t kEmptyRef = 0xFFFFFFFFu;  // leaf bit set, count 15, start 0x7FFFFFF: never reached (box is inverted)
+constexpr uint32_t kEmptyRef = 0x80000000u;  // leaf with zero triangles; its box is parked far away so the slab test fails
 constexpr int kLeafCountShift = 27;
 constexpr uint32_t kLeafStartMask = (1u << kLeafCountShift) - 1u;
 constexpr int kMaxLeafTris = 15;
@@ -45,7 +46,8 @@ struct DeviceScene {
     int32_t width, height;
     float cam[3], top_left[3], right[3], up[3];
     float inv_width, inv_height;
-    float min_coord[3], inv_dim[3];
+    float min_coord[3], inv_dim[3];          // the reference's key bounds (scene.cu:822-830), kept for completeness
+    float key_min[3], key_inv_extent[3];     // bounds used by reorder_key: triangle root box (or sphere bounds), 1/(max-min)
 };
 
 struct RayQueue {

@@ -1,0 +1,249 @@
+// Kernels of the render core. One translation unit (rt_core.cu) includes this file.
+//
+//   bounce_kernel    one bounce of the wavefront: [generate |  fetch] -> closest hit -> shade -> accumulate radiance
+//                    -> compact survivors into the next queue (+ optional reorder key). Persistent CTAs, warp-level
+//                    work fetch from a global cursor.                       (cuda_process_rays raytracing.cu:83-94,
+//                    cuda_generate_initial_rays :76-81, cuda_accumulate_rays :96-107, Scene::process_ray scene.cu:320-487)
+//   trace_kernel     closest hit only (parity hook for Scene::bvh_closest_hit_distance)
+//   generate_kernel / process_kernel   reference-layout hooks for Scene::generate_initial_rays / Scene::process_ray
+//   bloom_* / tonemap_kernel           raytracing.cu:21-74 / :286-303
+#pragma once
+
+#include "device_scene.cuh"
+#include "rng_math.cuh"
+#include "shade.cuh"
+#include "traverse.cuh"
+
+namespace rtd {
+
+constexpr int kBlock = 128;        // threads per CTA of the traversal kernels
+constexpr int kBlocksPerSM = 6;    // 6 x 32 KB of stack = 192 KB shared memory per SM, <= 85 registers per thread
+constexpr int kFetchRounds = 4;    // a warp claims 4 x 32 consecutive queue slots per atomic
+
+__device__ __forceinline__ uint32_t lanemask_lt() { return (1u << (threadIdx.x & 31)) - 1u; }
+
+__device__ __forceinline__ void add_radiance(float *framebuffer, uint32_t pixel, float3 c)
+{
+    if (c.x != 0.0f) atomicAdd(framebuffer + 3 * (size_t)pixel + 0, c.x);
+    if (c.y != 0.0f) atomicAdd(framebuffer + 3 * (size_t)pixel + 1, c.y);
+    if (c.z != 0.0f) atomicAdd(framebuffer + 3 * (size_t)pixel + 2, c.z);
+}
+
+template <bool FIRST, bool STATS>
+__global__ void __launch_bounds__(kBlock, kBlocksPerSM) bounce_kernel(const DeviceScene sc, const BounceArgs a)
+{
+    __shared__ SharedStack<kBlock> stack;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t n_in = FIRST ? a.n_first : a.pc->count[a.bounce];
+    uint32_t *cursor = &a.pc->cursor[a.bounce];
+    uint32_t *out_count = &a.pc->count[a.bounce + 1];
+    const bool write_out = a.out.qa != nullptr;
+    TraceCounters ctr;
+
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        atomicAdd(&a.totals->live_ray_bounces, (unsigned long long)n_in);
+        atomicAdd(&a.totals->live_per_bounce[a.bounce], (unsigned long long)n_in);
+    }
+
+    for (;;) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(cursor, 32u * kFetchRounds);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n_in) break;
+
+#pragma unroll 1
+        for (int round = 0; round < kFetchRounds; round++) {
+            const uint32_t first = base + 32u * round;
+            if (first >= n_in) break;
+            const uint32_t i = first + lane;
+            bool active = i < n_in;
+
+            float3 o = f3(0, 0, 0), d = f3(0, 0, 1), T = f3(1, 1, 1);
+            uint32_t id = i;
+            if (active) {
+                if (FIRST) {
+                    active = generate_ray(sc, id, a.rays_per_pixel, a.gen_seed, a.pcg_inc, o, d);
+                } else {
+                    const uint32_t slot = a.order ? __ldg(a.order + i) : i;
+                    const float4 ra = a.in.qa[slot], rb = a.in.qb[slot];
+                    const float2 rc = a.in.qc[slot];
+                    o = f3(ra.x, ra.y, ra.z);
+                    d = f3(ra.w, rb.x, rb.y);
+                    T = f3(rb.z, rb.w, rc.x);
+                    id = __float_as_uint(rc.y);
+                }
+            }
+
+            bool alive = false;
+            if (active) {
+                float closest = kMissT;
+                int prim = -1;
+                intersect_spheres(sc, o, d, closest, prim);
+                traverse_bvh<kBlock, STATS>(sc, o, d, closest, prim, stack, ctr);
+
+                const uint32_t pixel = id / (uint32_t)a.rays_per_pixel;
+                if (prim < 0) {
+                    add_radiance(a.framebuffer, pixel, shade_miss(sc, d) * T);
+                } else {
+                    Pcg rng = pcg_seed(id * 4137874753u + a.proc_seed, a.pcg_inc);  // raytracing.cu:89 with slot == ray id
+                    float3 emitted;
+                    shade_hit(sc, o, d, closest, prim, T, rng, emitted);
+                    add_radiance(a.framebuffer, pixel, emitted);
+                    alive = !is_zero(T);  // a path dies only when its throughput is exactly zero (Q10)
+                }
+            }
+
+            if (write_out) {  // next-bounce compaction: one atomic per warp, survivors stay contiguous
+                const uint32_t mask = __ballot_sync(0xffffffffu, alive);
+                if (mask) {
+                    uint32_t pos = 0;
+                    if (lane == 0) pos = atomicAdd(out_count, (uint32_t)__popc(mask));
+                    pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(mask & lanemask_lt());
+                    if (alive) {
+                        a.out.qa[pos] = make_float4(o.x, o.y, o.z, d.x);
+                        a.out.qb[pos] = make_float4(d.y, d.z, T.x, T.y);
+                        a.out.qc[pos] = make_float2(T.z, __uint_as_float(id));
+                        if (a.keys_out) a.keys_out[pos] = reorder_key(sc.key_min, sc.key_inv_extent, o, d, a.key_bits);
+                    }
+                }
+            }
+        }
+    }
+
+    if (STATS) {
+        uint32_t iv = ctr.internal_visits, tt = ctr.triangle_tests;
+        for (int off = 16; off > 0; off >>= 1) {
+            iv += __shfl_xor_sync(0xffffffffu, iv, off);
+            tt += __shfl_xor_sync(0xffffffffu, tt, off);
+        }
+        if (lane == 0) {
+            atomicAdd(&a.totals->internal_visits, (unsigned long long)iv);
+            atomicAdd(&a.totals->triangle_tests, (unsigned long long)tt);
+        }
+    }
+}
+
+// ---- parity hooks: same device functions, reference-layout I/O ---------------------------------------------------
+
+template <bool STATS>
+__global__ void __launch_bounds__(kBlock, kBlocksPerSM) trace_kernel(const DeviceScene sc, const float *__restrict__ rays6, uint32_t n,
+                                                                      int with_spheres, int *__restrict__ out_prim,
+                                                                      float *__restrict__ out_t, RenderTotals *totals)
+{
+    __shared__ SharedStack<kBlock> stack;
+    TraceCounters ctr;
+    for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n; i += gridDim.x * kBlock) {
+        const float *r = rays6 + 6 * (size_t)i;
+        float3 o = f3(r[0], r[1], r[2]), d = f3(r[3], r[4], r[5]);
+        float closest = kMissT;
+        int prim = -1;
+        if (with_spheres) intersect_spheres(sc, o, d, closest, prim);
+        traverse_bvh<kBlock, STATS>(sc, o, d, closest, prim, stack, ctr);
+        out_prim[i] = prim;
+        out_t[i] = closest;
+    }
+    if (STATS) {
+        atomicAdd(&totals->internal_visits, (unsigned long long)ctr.internal_visits);
+        atomicAdd(&totals->triangle_tests, (unsigned long long)ctr.triangle_tests);
+    }
+}
+
+// 12 floats per ray: origin, direction, transmitted = 1, collected = 0 (RayData, scene.cuh:61-68)
+__global__ void generate_kernel(const DeviceScene sc, int rays_per_pixel, uint32_t first, uint32_t n, uint32_t gen_seed,
+                                unsigned long long inc, float *__restrict__ out12)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float3 o, d;
+    float *r = out12 + 12 * (size_t)i;
+    if (!generate_ray(sc, first + i, rays_per_pixel, gen_seed, inc, o, d)) return;
+    r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = d.x; r[4] = d.y; r[5] = d.z;
+    r[6] = r[7] = r[8] = 1.0f;
+    r[9] = r[10] = r[11] = 0.0f;
+}
+
+// One process_ray step on reference-layout records, rng = xor_srand(seeds[i]); in place.
+__global__ void __launch_bounds__(kBlock, kBlocksPerSM) process_kernel(const DeviceScene sc, float *__restrict__ data12,
+                                                                        const uint32_t *__restrict__ seeds, uint32_t n,
+                                                                        unsigned long long inc)
+{
+    __shared__ SharedStack<kBlock> stack;
+    TraceCounters ctr;
+    for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n; i += gridDim.x * kBlock) {
+        float *r = data12 + 12 * (size_t)i;
+        float3 o = f3(r[0], r[1], r[2]), d = f3(r[3], r[4], r[5]), T = f3(r[6], r[7], r[8]), C = f3(r[9], r[10], r[11]);
+        if (is_zero(T)) continue;  // dead ray early-out (scene.cu:323-328)
+        float closest = kMissT;
+        int prim = -1;
+        intersect_spheres(sc, o, d, closest, prim);
+        traverse_bvh<kBlock, false>(sc, o, d, closest, prim, stack, ctr);
+        if (prim < 0) {
+            C = C + shade_miss(sc, d) * T;
+            T = f3(0, 0, 0);
+        } else {
+            Pcg rng = pcg_seed(seeds[i], inc);
+            float3 emitted;
+            shade_hit(sc, o, d, closest, prim, T, rng, emitted);
+            C = C + emitted;
+        }
+        r[0] = o.x; r[1] = o.y; r[2] = o.z; r[3] = d.x; r[4] = d.y; r[5] = d.z;
+        r[6] = T.x; r[7] = T.y; r[8] = T.z; r[9] = C.x; r[10] = C.y; r[11] = C.z;
+    }
+}
+
+// ---- post-process: bloom (raytracing.cu:21-74,360-392) and tone map (:286-303) ------------------------------------
+// The reference runs four kernels (high-pass, H blur, V blur, add); here the high-pass is folded into the H blur's
+// taps and the add into the V blur. Tap order and arithmetic are the reference's, so results are bit-identical to the
+// host oracle (products that feed a compare are kept un-contracted).
+
+__device__ __forceinline__ float3 load3(const float *p, size_t i) { return f3(p[3 * i], p[3 * i + 1], p[3 * i + 2]); }
+
+__global__ void bloom_h_kernel(const float *__restrict__ image, float *__restrict__ tmp, float threshold, int width, int height)
+{
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= width * height) return;
+    int x = idx % width, y = idx / width;
+    float3 sum = f3(0, 0, 0);
+    int count = 0;
+    for (int dx = -5; dx <= 5; dx++) {
+        int nx = x + dx;
+        if (nx < 0 || nx >= width) continue;
+        float3 p = load3(image, (size_t)y * width + nx);
+        float lum = dot_nofma(p, f3(0.2126f, 0.7152f, 0.0722f));
+        if (lum > threshold) sum = sum + p;  // adding (0,0,0) for dim taps is a no-op except -0 -> +0, never produced here
+        count++;
+    }
+    float w = 1.0f / (float)count;
+    tmp[3 * (size_t)idx] = w * sum.x; tmp[3 * (size_t)idx + 1] = w * sum.y; tmp[3 * (size_t)idx + 2] = w * sum.z;
+}
+
+__global__ void bloom_v_add_kernel(const float *__restrict__ tmp, const float *__restrict__ image, float *__restrict__ out, int width,
+                                   int height)
+{
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= width * height) return;
+    int x = idx % width, y = idx / width;
+    float3 sum = f3(0, 0, 0);
+    int count = 0;
+    for (int dy = -5; dy <= 5; dy++) {
+        int ny = y + dy;
+        if (ny < 0 || ny >= height) continue;
+        sum = sum + load3(tmp, (size_t)ny * width + x);
+        count++;
+    }
+    float w = 1.0f / (float)count;
+    float3 p = load3(image, (size_t)idx);
+    out[3 * (size_t)idx] = p.x + __fmul_rn(w, sum.x);
+    out[3 * (size_t)idx + 1] = p.y + __fmul_rn(w, sum.y);
+    out[3 * (size_t)idx + 2] = p.z + __fmul_rn(w, sum.z);
+}
+
+__global__ void tonemap_kernel(const float *__restrict__ image, uint8_t *__restrict__ out, float scale, size_t n)
+{
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float c = __fmul_rn(scale, image[i]);
+    out[i] = (uint8_t)(sqrtf(c / (c + 1.0f)) * 255.999f);
+}
+
+}  // namespace rtd

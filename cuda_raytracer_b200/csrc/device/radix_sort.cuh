@@ -1,0 +1,162 @@
+// Hand-written stable LSD radix sort of (key u32, value u32) pairs, 8 bits per digit pass. Replaces the reference's
+// cub::DeviceRadixSort::SortPairs (raytracing.cu:194-195,240-246) as the ray-reordering pass.
+//
+// Structure ("one sweep per digit"):
+//   1. sort_histogram_kernel: ONE read of the keys builds the global histograms of every digit position.
+//   2. sort_scan_kernel: exclusive scan of each 256-bin histogram (tiny).
+//   3. sort_scatter_kernel, once per digit: each CTA takes the next tile (dynamic tile id), ranks its keys stably
+//      (warp match + per-warp counters in shared memory), obtains its global offset per digit by decoupled look-back
+//      over the tile-status array, and scatters keys and values. 8 B read + 8 B written per pair per digit.
+//
+// The element count lives in DEVICE memory (it is the live-ray count produced by the previous bounce kernel), so the
+// host launches for an upper bound and surplus CTAs retire immediately: no host synchronisation inside a pass.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace rtd {
+
+constexpr int kSortBlock = 256;
+constexpr int kSortItems = 16;                          // keys per thread
+constexpr int kSortTile = kSortBlock * kSortItems;      // 4096 keys per tile
+constexpr int kSortWarps = kSortBlock / 32;
+constexpr int kSortMaxPasses = 4;
+constexpr uint32_t kFlagAggregate = 1u << 30;           // tile status: local count published
+constexpr uint32_t kFlagPrefix = 2u << 30;              // tile status: inclusive prefix published
+constexpr uint32_t kFlagMask = 3u << 30;
+constexpr uint32_t kValueMask = ~kFlagMask;
+
+struct SortArgs {
+    const uint32_t *count_ptr;   // device: number of pairs
+    uint32_t *hist;              // [kSortMaxPasses][256] global digit histograms -> exclusive offsets after the scan
+    uint32_t *tile_status;       // [passes][max_tiles][256]
+    uint32_t *tile_counter;      // [passes] dynamic tile ids
+    int passes;
+    uint32_t max_tiles;
+};
+
+__global__ void __launch_bounds__(kSortBlock) sort_histogram_kernel(const uint32_t *__restrict__ keys, SortArgs s)
+{
+    __shared__ uint32_t h[kSortMaxPasses][256];
+    for (int p = 0; p < s.passes; p++) h[p][threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t n = *s.count_ptr;
+    for (uint32_t i = blockIdx.x * kSortBlock + threadIdx.x; i < n; i += gridDim.x * kSortBlock) {
+        uint32_t k = keys[i];
+        for (int p = 0; p < s.passes; p++) atomicAdd(&h[p][(k >> (8 * p)) & 255u], 1u);
+    }
+    __syncthreads();
+    for (int p = 0; p < s.passes; p++) {
+        uint32_t v = h[p][threadIdx.x];
+        if (v) atomicAdd(&s.hist[p * 256 + threadIdx.x], v);
+    }
+}
+
+// one CTA of 256 threads per digit position: exclusive scan in place
+__global__ void __launch_bounds__(256) sort_scan_kernel(SortArgs s)
+{
+    __shared__ uint32_t warp_sum[8];
+    uint32_t *h = s.hist + blockIdx.x * 256;
+    uint32_t v = h[threadIdx.x], incl = v;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    for (int off = 1; off < 32; off <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= (uint32_t)off) incl += t;
+    }
+    if (lane == 31) warp_sum[warp] = incl;
+    __syncthreads();
+    uint32_t base = 0;
+    for (uint32_t w = 0; w < warp; w++) base += warp_sum[w];
+    h[threadIdx.x] = base + incl - v;
+}
+
+// One digit pass. values_in == nullptr means "value = element index" (first pass of a fresh permutation).
+__global__ void __launch_bounds__(kSortBlock) sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ values_in,
+                                                                   uint32_t *__restrict__ keys_out, uint32_t *__restrict__ values_out,
+                                                                   SortArgs s, int pass)
+{
+    __shared__ uint32_t warp_hist[kSortWarps][256];
+    __shared__ uint32_t digit_base[256];
+    __shared__ uint32_t tile_id_sh;
+
+    const uint32_t n = *s.count_ptr;
+    const uint32_t num_tiles = (n + kSortTile - 1) / kSortTile;
+    if (threadIdx.x == 0) tile_id_sh = atomicAdd(&s.tile_counter[pass], 1u);
+    for (int w = 0; w < kSortWarps; w++) warp_hist[w][threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t tile = tile_id_sh;
+    if (tile >= num_tiles) return;
+
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t shift = 8u * pass;
+    const uint32_t warp_base = tile * kSortTile + warp * (kSortItems * 32u);
+    const uint32_t lt = (1u << lane) - 1u;
+
+    uint32_t key[kSortItems], val[kSortItems];
+    uint16_t rank[kSortItems];
+#pragma unroll
+    for (int r = 0; r < kSortItems; r++) {
+        uint32_t i = warp_base + r * 32u + lane;
+        bool valid = i < n;
+        key[r] = valid ? keys_in[i] : 0xFFFFFFFFu;
+        val[r] = valid ? (values_in ? values_in[i] : i) : 0u;
+    }
+    // stable ranking inside the warp's 512-key segment: rounds in memory order, lanes in order within a round
+#pragma unroll
+    for (int r = 0; r < kSortItems; r++) {
+        uint32_t i = warp_base + r * 32u + lane;
+        bool valid = i < n;
+        uint32_t digit = (key[r] >> shift) & 255u;
+        uint32_t peers = __match_any_sync(0xffffffffu, valid ? digit : (256u + lane));
+        uint32_t leader = __ffs(peers) - 1;
+        uint32_t before = 0;
+        if (valid && lane == leader) {
+            before = warp_hist[warp][digit];
+            warp_hist[warp][digit] = before + __popc(peers);
+        }
+        before = __shfl_sync(0xffffffffu, before, leader);
+        rank[r] = (uint16_t)(before + __popc(peers & lt));
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // thread d owns digit d: exclusive scan over the 8 warps, tile total, then decoupled look-back
+    const uint32_t dgt = threadIdx.x;
+    uint32_t running = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; w++) {
+        uint32_t c = warp_hist[w][dgt];
+        warp_hist[w][dgt] = running;
+        running += c;
+    }
+    volatile uint32_t *status = s.tile_status + ((size_t)pass * s.max_tiles) * 256u;
+    uint32_t exclusive = 0;
+    if (tile == 0) {
+        status[dgt] = running | kFlagPrefix;
+    } else {
+        status[(size_t)tile * 256u + dgt] = running | kFlagAggregate;
+        for (int t = (int)tile - 1; t >= 0; t--) {
+            uint32_t st;
+            do { st = status[(size_t)t * 256u + dgt]; } while ((st & kFlagMask) == 0u);
+            exclusive += st & kValueMask;
+            if (st & kFlagPrefix) break;
+        }
+        status[(size_t)tile * 256u + dgt] = (exclusive + running) | kFlagPrefix;
+    }
+    digit_base[dgt] = s.hist[pass * 256 + dgt] + exclusive;
+    __syncthreads();
+
+#pragma unroll
+    for (int r = 0; r < kSortItems; r++) {
+        uint32_t i = warp_base + r * 32u + lane;
+        if (i < n) {
+            uint32_t digit = (key[r] >> shift) & 255u;
+            uint32_t pos = digit_base[digit] + warp_hist[warp][digit] + rank[r];
+            keys_out[pos] = key[r];
+            values_out[pos] = val[r];
+        }
+    }
+}
+
+}  // namespace rtd

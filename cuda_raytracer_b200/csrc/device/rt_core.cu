@@ -1,0 +1,700 @@
+// librtcore device side: context, scene packing/upload, the pass loop and the C ABI of include/rt_core.h.
+// Replaces gpu_raytrace and its helpers (/root/reference/raytracing.cu:170-284, scene.cu:243-278).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../../include/rt_core.h"
+#include "kernels.cuh"
+#include "radix_sort.cuh"
+
+namespace rt {
+void set_global_error(const std::string &msg);  // scene_api.cpp
+const char *global_error();
+}  // namespace rt
+
+using namespace rtd;
+
+struct rt_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    std::string error;
+
+    // scene
+    bool has_scene = false;
+    DeviceScene ds{};
+    void *d_nodes = nullptr, *d_tris = nullptr, *d_materials = nullptr, *d_spheres = nullptr, *d_env = nullptr, *d_matidx = nullptr;
+    int ray_count = 0, bounces = 0;
+    float exposure = 0;
+    int packed_nodes = 0, packed_depth = 0;
+
+    // render state
+    float *d_fb = nullptr, *d_fb_tmp = nullptr, *d_fb_tmp2 = nullptr;
+    uint8_t *d_rgb8 = nullptr;
+    size_t fb_pixels = 0;
+    RayQueue queue[2] = {};
+    size_t queue_capacity = 0;
+    uint32_t *d_keys[2] = {nullptr, nullptr}, *d_vals[2] = {nullptr, nullptr};
+    size_t sort_capacity = 0;
+    uint32_t *d_sort_scratch = nullptr;  // hist + tile counters + tile status
+    size_t sort_scratch_words = 0;
+    PassCounters *d_pc = nullptr;
+    RenderTotals *d_totals = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+};
+
+namespace {
+
+int fail(rt_ctx *ctx, int status, const std::string &msg)
+{
+    if (ctx) ctx->error = msg;
+    rt::set_global_error(msg);
+    return status;
+}
+
+#define RT_CUDA(ctx, call)                                                                                   \
+    do {                                                                                                     \
+        cudaError_t e_ = (call);                                                                             \
+        if (e_ != cudaSuccess)                                                                               \
+            return fail(ctx, e_ == cudaErrorMemoryAllocation ? RT_ERR_NOMEM : RT_ERR_CUDA,                   \
+                        std::string(#call) + ": " + cudaGetErrorString(e_));                                 \
+    } while (0)
+
+template <typename T>
+void release(T *&p)
+{
+    if (p) cudaFree(p);
+    p = nullptr;
+}
+
+// ---- BVH packing: reference 32-byte nodes -> 64-byte two-child records (layout in device_scene.cuh) --------------
+struct RefNode {  // scene.cuh:82-100
+    float lo[3], hi[3];
+    int32_t child1, child2;
+};
+static_assert(sizeof(RefNode) == 32, "reference node layout");
+
+struct PackedRecord {
+    float f[12];
+    uint32_t ref[4];
+};
+static_assert(sizeof(PackedRecord) == 64, "packed record");
+
+struct Packer {
+    const RefNode *nodes;
+    std::vector<PackedRecord> out;
+    int max_depth = 0;
+
+    static void set_box(PackedRecord &r, int child, const float *lo, const float *hi)
+    {
+        float *b = r.f + 6 * child;
+        b[0] = lo[0]; b[1] = lo[1]; b[2] = lo[2];
+        b[3] = hi[0]; b[4] = hi[1]; b[5] = hi[2];
+    }
+    static void set_empty(PackedRecord &r, int child)
+    {
+        const float far_away[3] = {3e38f, 3e38f, 3e38f};
+        set_box(r, child, far_away, far_away);
+        r.ref[child] = kEmptyRef;
+    }
+    // triangles [begin, end) under box lo/hi -> a leaf ref, or a chain of same-box records when there are > 15
+    uint32_t range_ref(int begin, int end, const float *lo, const float *hi, int depth)
+    {
+        int count = end - begin;
+        if (count <= 0) return kEmptyRef;
+        if (count <= kMaxLeafTris) return kLeafBit | ((uint32_t)count << kLeafCountShift) | (uint32_t)begin;
+        max_depth = std::max(max_depth, depth + 1);
+        size_t idx = out.size();
+        out.emplace_back();
+        int mid = begin + (count + 1) / 2;
+        uint32_t a = range_ref(begin, mid, lo, hi, depth + 1);
+        uint32_t b = range_ref(mid, end, lo, hi, depth + 1);
+        set_box(out[idx], 0, lo, hi);
+        set_box(out[idx], 1, lo, hi);
+        out[idx].ref[0] = a;
+        out[idx].ref[1] = b;
+        return (uint32_t)idx;
+    }
+    uint32_t node_ref(int i, int depth)
+    {
+        const RefNode &n = nodes[i];
+        if (n.child2 <= n.child1) return range_ref(n.child2, n.child1, n.lo, n.hi, depth);  // leaf: [child2, child1)
+        max_depth = std::max(max_depth, depth + 1);
+        size_t idx = out.size();
+        out.emplace_back();
+        uint32_t a = node_ref(n.child1, depth + 1);
+        uint32_t b = node_ref(n.child2, depth + 1);
+        PackedRecord &r = out[idx];
+        set_box(r, 0, nodes[n.child1].lo, nodes[n.child1].hi);
+        set_box(r, 1, nodes[n.child2].lo, nodes[n.child2].hi);
+        r.ref[0] = a;
+        r.ref[1] = b;
+        if (a == kEmptyRef) set_empty(r, 0);
+        if (b == kEmptyRef) set_empty(r, 1);
+        return (uint32_t)idx;
+    }
+    void run(int node_count)
+    {
+        out.clear();
+        out.reserve((size_t)node_count / 2 + 2);
+        bool root_internal = node_count > 0 && nodes[0].child2 > nodes[0].child1;
+        if (root_internal) {
+            node_ref(0, 0);
+        } else {  // root is a leaf (<= 4 triangles, no_bvh, or no triangles at all): synthesise record 0
+            out.emplace_back();
+            max_depth = 1;
+            uint32_t a = node_count > 0 ? range_ref(nodes[0].child2, nodes[0].child1, nodes[0].lo, nodes[0].hi, 1) : kEmptyRef;
+            if (a == kEmptyRef) set_empty(out[0], 0);
+            else { set_box(out[0], 0, nodes[0].lo, nodes[0].hi); out[0].ref[0] = a; }
+            set_empty(out[0], 1);
+        }
+    }
+};
+
+int upload(rt_ctx *ctx, void **dst, const void *src, size_t bytes)
+{
+    release(*dst);
+    RT_CUDA(ctx, cudaMalloc(dst, std::max<size_t>(bytes, 16)));
+    if (bytes) RT_CUDA(ctx, cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return RT_OK;
+}
+
+void copy3(float *dst, const float *src) { dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2]; }
+
+int set_image_block(rt_ctx *ctx, const rt_scene_desc *s)
+{
+    if (s->width <= 0 || s->height <= 0 || s->ray_count < 0 || s->bounces < 0 || s->bounces > 32)
+        return fail(ctx, RT_ERR_INVALID, "image block: need width,height > 0, ray_count >= 0, 0 <= bounces <= 32");
+    DeviceScene &d = ctx->ds;
+    d.width = s->width;
+    d.height = s->height;
+    copy3(d.cam, s->camera_position);
+    copy3(d.top_left, s->near_plane_top_left);
+    copy3(d.right, s->scaled_right);
+    copy3(d.up, s->scaled_up);
+    d.inv_width = s->inv_width;
+    d.inv_height = s->inv_height;
+    ctx->ray_count = s->ray_count;
+    ctx->bounces = s->bounces;
+    ctx->exposure = s->exposure;
+    return RT_OK;
+}
+
+}  // namespace
+
+// ---- context ----------------------------------------------------------------------------------------------------
+extern "C" int rt_api_version(void) { return RT_API_VERSION; }
+
+extern "C" int rt_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" const char *rt_last_error(const rt_ctx *ctx) { return ctx ? ctx->error.c_str() : rt::global_error(); }
+
+extern "C" int rt_create(rt_ctx **out, int device)
+{
+    if (!out) return fail(nullptr, RT_ERR_INVALID, "rt_create: null out pointer");
+    *out = nullptr;
+    int n = rt_device_count();
+    if (n <= 0) return fail(nullptr, RT_ERR_NO_DEVICE, "rt_create: no CUDA device available (this library has no CPU fallback)");
+    if (device < 0 || device >= n) return fail(nullptr, RT_ERR_NO_DEVICE, "rt_create: device index out of range");
+    rt_ctx *ctx = new rt_ctx();
+    ctx->device = device;
+    RT_CUDA(ctx, cudaSetDevice(device));
+    cudaDeviceProp prop;
+    RT_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
+    ctx->sm_count = prop.multiProcessorCount;
+    RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    RT_CUDA(ctx, cudaEventCreate(&ctx->ev_start));
+    RT_CUDA(ctx, cudaEventCreate(&ctx->ev_stop));
+    RT_CUDA(ctx, cudaMalloc(&ctx->d_pc, sizeof(PassCounters)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->d_totals, sizeof(RenderTotals)));
+    *out = ctx;
+    return RT_OK;
+}
+
+extern "C" void rt_destroy(rt_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    release(ctx->d_nodes); release(ctx->d_tris); release(ctx->d_materials); release(ctx->d_spheres); release(ctx->d_env);
+    release(ctx->d_matidx); release(ctx->d_fb); release(ctx->d_fb_tmp); release(ctx->d_fb_tmp2); release(ctx->d_rgb8);
+    for (int i = 0; i < 2; i++) {
+        release(ctx->queue[i].qa); release(ctx->queue[i].qb); release(ctx->queue[i].qc);
+        release(ctx->d_keys[i]); release(ctx->d_vals[i]);
+    }
+    release(ctx->d_sort_scratch); release(ctx->d_pc); release(ctx->d_totals);
+    if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
+    if (ctx->ev_stop) cudaEventDestroy(ctx->ev_stop);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" int rt_scene_set_image(rt_ctx *ctx, const rt_scene_desc *s)
+{
+    if (!ctx || !s) return fail(ctx, RT_ERR_INVALID, "rt_scene_set_image: null argument");
+    if (!ctx->has_scene) return fail(ctx, RT_ERR_INVALID, "rt_scene_set_image: no scene uploaded");
+    return set_image_block(ctx, s);
+}
+
+extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *s)
+{
+    if (!ctx || !s) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: null argument");
+    if (s->sphere_count < 0 || s->triangle_count < 0 || s->material_count <= 0 || s->bvh_node_count <= 0 || !s->bvh_nodes ||
+        !s->materials || !s->environment_map || s->env_width <= 0 || s->env_height <= 0 ||
+        (s->triangle_count > 0 && !s->triangles) || (s->sphere_count > 0 && !s->spheres) ||
+        (s->triangle_count + s->sphere_count > 0 && !s->material_indices))
+        return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: malformed scene descriptor");
+    if ((uint32_t)s->triangle_count > kLeafStartMask) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: more than 2^27 triangles");
+    RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    ctx->has_scene = false;
+    int rc = set_image_block(ctx, s);
+    if (rc != RT_OK) return rc;
+
+    Packer packer;
+    packer.nodes = static_cast<const RefNode *>(s->bvh_nodes);
+    packer.run(s->bvh_node_count);
+    if (packer.max_depth > kStackDepth) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: BVH deeper than the traversal stack (32)");
+    ctx->packed_nodes = (int)packer.out.size();
+    ctx->packed_depth = packer.max_depth;
+
+    // triangles: {p1|n.x} {e1|n.y} {e2|n.z}
+    std::vector<float> tri4((size_t)s->triangle_count * 12);
+    for (int i = 0; i < s->triangle_count; i++) {
+        const float *t = s->triangles + 12 * (size_t)i;
+        float *o = &tri4[12 * (size_t)i];
+        for (int k = 0; k < 3; k++) {
+            o[4 * k + 0] = t[3 * k + 0]; o[4 * k + 1] = t[3 * k + 1]; o[4 * k + 2] = t[3 * k + 2];
+            o[4 * k + 3] = t[9 + k];
+        }
+    }
+    size_t texels = (size_t)s->env_width * s->env_height;
+    std::vector<float> env4(texels * 4);
+    for (size_t i = 0; i < texels; i++) {
+        env4[4 * i] = s->environment_map[3 * i]; env4[4 * i + 1] = s->environment_map[3 * i + 1];
+        env4[4 * i + 2] = s->environment_map[3 * i + 2]; env4[4 * i + 3] = 0.0f;
+    }
+    int prims = s->sphere_count + s->triangle_count;
+    if ((rc = upload(ctx, &ctx->d_nodes, packer.out.data(), packer.out.size() * sizeof(PackedRecord))) != RT_OK) return rc;
+    if ((rc = upload(ctx, &ctx->d_tris, tri4.data(), tri4.size() * sizeof(float))) != RT_OK) return rc;
+    if ((rc = upload(ctx, &ctx->d_materials, s->materials, (size_t)s->material_count * 48)) != RT_OK) return rc;
+    if ((rc = upload(ctx, &ctx->d_spheres, s->spheres, (size_t)s->sphere_count * 16)) != RT_OK) return rc;
+    if ((rc = upload(ctx, &ctx->d_env, env4.data(), env4.size() * sizeof(float))) != RT_OK) return rc;
+    if ((rc = upload(ctx, &ctx->d_matidx, s->material_indices, (size_t)prims * sizeof(uint16_t))) != RT_OK) return rc;
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // staging vectors die at return
+
+    DeviceScene &d = ctx->ds;
+    d.nodes = static_cast<const float4 *>(ctx->d_nodes);
+    d.tris = static_cast<const float4 *>(ctx->d_tris);
+    d.materials = static_cast<const float4 *>(ctx->d_materials);
+    d.spheres = static_cast<const float4 *>(ctx->d_spheres);
+    d.env = static_cast<const float4 *>(ctx->d_env);
+    d.material_indices = static_cast<const uint16_t *>(ctx->d_matidx);
+    d.sphere_count = s->sphere_count;
+    d.tri_count = s->triangle_count;
+    d.env_w = s->env_width;
+    d.env_h = s->env_height;
+    copy3(d.min_coord, s->min_coord);
+    copy3(d.inv_dim, s->inv_dimensions);
+
+    // bounds for the reorder key: the triangle root box, else the spheres' bounds
+    const RefNode &root = packer.nodes[0];
+    float lo[3], hi[3];
+    if (s->triangle_count > 0) { copy3(lo, root.lo); copy3(hi, root.hi); }
+    else {
+        for (int k = 0; k < 3; k++) { lo[k] = 1e30f; hi[k] = -1e30f; }
+        for (int i = 0; i < s->sphere_count; i++)
+            for (int k = 0; k < 3; k++) {
+                float c = s->spheres[4 * i + k], r = std::min(s->spheres[4 * i + 3], 1e3f);
+                lo[k] = std::min(lo[k], c - r); hi[k] = std::max(hi[k], c + r);
+            }
+    }
+    for (int k = 0; k < 3; k++) {
+        float extent = hi[k] - lo[k];
+        d.key_min[k] = lo[k];
+        d.key_inv_extent[k] = (extent > 0.0f && extent < 1e30f) ? 1.0f / extent : 0.0f;
+    }
+    ctx->has_scene = true;
+    return RT_OK;
+}
+
+namespace {
+
+int ensure_framebuffer(rt_ctx *ctx)
+{
+    size_t px = (size_t)ctx->ds.width * ctx->ds.height;
+    if (px == ctx->fb_pixels && ctx->d_fb) return RT_OK;
+    release(ctx->d_fb); release(ctx->d_fb_tmp); release(ctx->d_fb_tmp2); release(ctx->d_rgb8);
+    ctx->fb_pixels = 0;
+    RT_CUDA(ctx, cudaMalloc(&ctx->d_fb, px * 3 * sizeof(float)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->d_fb_tmp, px * 3 * sizeof(float)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->d_fb_tmp2, px * 3 * sizeof(float)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->d_rgb8, px * 3));
+    RT_CUDA(ctx, cudaMemsetAsync(ctx->d_fb, 0, px * 3 * sizeof(float), ctx->stream));
+    ctx->fb_pixels = px;
+    return RT_OK;
+}
+
+int ensure_queues(rt_ctx *ctx, size_t rays, bool sort)
+{
+    if (rays > ctx->queue_capacity) {
+        for (int i = 0; i < 2; i++) { release(ctx->queue[i].qa); release(ctx->queue[i].qb); release(ctx->queue[i].qc); }
+        ctx->queue_capacity = 0;
+        for (int i = 0; i < 2; i++) {
+            RT_CUDA(ctx, cudaMalloc(&ctx->queue[i].qa, rays * sizeof(float4)));
+            RT_CUDA(ctx, cudaMalloc(&ctx->queue[i].qb, rays * sizeof(float4)));
+            RT_CUDA(ctx, cudaMalloc(&ctx->queue[i].qc, rays * sizeof(float2)));
+        }
+        ctx->queue_capacity = rays;
+    }
+    if (sort && rays > ctx->sort_capacity) {
+        for (int i = 0; i < 2; i++) { release(ctx->d_keys[i]); release(ctx->d_vals[i]); }
+        release(ctx->d_sort_scratch);
+        ctx->sort_capacity = 0;
+        for (int i = 0; i < 2; i++) {
+            RT_CUDA(ctx, cudaMalloc(&ctx->d_keys[i], rays * sizeof(uint32_t)));
+            RT_CUDA(ctx, cudaMalloc(&ctx->d_vals[i], rays * sizeof(uint32_t)));
+        }
+        size_t tiles = (rays + kSortTile - 1) / kSortTile;
+        ctx->sort_scratch_words = (size_t)kSortMaxPasses * 256 + 16 + (size_t)kSortMaxPasses * tiles * 256;
+        RT_CUDA(ctx, cudaMalloc(&ctx->d_sort_scratch, ctx->sort_scratch_words * sizeof(uint32_t)));
+        ctx->sort_capacity = rays;
+    }
+    return RT_OK;
+}
+
+// Enqueue a stable sort of (keys[0], index) on the low `bits` bits; n is read from *count_ptr on the device, `bound`
+// is the host-side upper bound used for grid sizing. On return *sorted_vals points at the permutation.
+int enqueue_sort(rt_ctx *ctx, const uint32_t *count_ptr, size_t bound, int bits, bool iota, uint32_t **sorted_keys,
+                 uint32_t **sorted_vals, int *launches)
+{
+    int passes = std::min(kSortMaxPasses, std::max(1, (bits + 7) / 8));
+    size_t tiles = (ctx->sort_capacity + kSortTile - 1) / kSortTile;
+    uint32_t launch_tiles = (uint32_t)((bound + kSortTile - 1) / kSortTile);
+    SortArgs s;
+    s.count_ptr = count_ptr;
+    s.hist = ctx->d_sort_scratch;
+    s.tile_counter = ctx->d_sort_scratch + kSortMaxPasses * 256;
+    s.tile_status = ctx->d_sort_scratch + kSortMaxPasses * 256 + 16;
+    s.passes = passes;
+    s.max_tiles = (uint32_t)tiles;
+    // zero histograms, tile counters and the status words of the tiles this launch can touch
+    RT_CUDA(ctx, cudaMemsetAsync(ctx->d_sort_scratch, 0, (kSortMaxPasses * 256 + 16) * sizeof(uint32_t), ctx->stream));
+    for (int p = 0; p < passes; p++)
+        RT_CUDA(ctx, cudaMemsetAsync(s.tile_status + (size_t)p * tiles * 256, 0, (size_t)launch_tiles * 256 * sizeof(uint32_t), ctx->stream));
+    int hist_blocks = (int)std::min<size_t>((size_t)ctx->sm_count * 8, std::max<size_t>(1, (bound + kSortBlock - 1) / kSortBlock));
+    sort_histogram_kernel<<<hist_blocks, kSortBlock, 0, ctx->stream>>>(ctx->d_keys[0], s);
+    sort_scan_kernel<<<passes, 256, 0, ctx->stream>>>(s);
+    int src = 0;
+    for (int p = 0; p < passes; p++) {
+        sort_scatter_kernel<<<launch_tiles, kSortBlock, 0, ctx->stream>>>(ctx->d_keys[src], (p == 0 && iota) ? nullptr : ctx->d_vals[src],
+                                                                          ctx->d_keys[src ^ 1], ctx->d_vals[src ^ 1], s, p);
+        src ^= 1;
+    }
+    RT_CUDA(ctx, cudaGetLastError());
+    *sorted_keys = ctx->d_keys[src];
+    *sorted_vals = ctx->d_vals[src];
+    if (launches) *launches += 2 + passes;
+    return RT_OK;
+}
+
+}  // namespace
+
+// ---- the pass loop (gpu_raytrace, raytracing.cu:170-284) ------------------------------------------------------
+namespace {
+
+template <bool FIRST>
+void launch_bounce(bool stats, int grid, cudaStream_t stream, const DeviceScene &ds, const BounceArgs &a)
+{
+    if (stats) bounce_kernel<FIRST, true><<<grid, kBlock, 0, stream>>>(ds, a);
+    else bounce_kernel<FIRST, false><<<grid, kBlock, 0, stream>>>(ds, a);
+}
+
+int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
+{
+    if (!ctx) return fail(nullptr, RT_ERR_INVALID, "rt_render: null context");
+    if (!ctx->has_scene) return fail(ctx, RT_ERR_INVALID, "rt_render: no scene uploaded");
+    auto wall0 = std::chrono::high_resolution_clock::now();
+    rt_render_opts opts{};
+    if (opts_in) opts = *opts_in;
+    opts.sort = opts_in ? opts_in->sort : 1;
+    const int pass_spp = opts.pass_spp > 0 ? opts.pass_spp : 20;  // MAX_RAYS_PER_PIXEL_PER_PASS, raytracing.cu:109
+    const size_t pixels = (size_t)ctx->ds.width * ctx->ds.height;
+    if (pixels * (size_t)pass_spp >= (1ull << 31)) return fail(ctx, RT_ERR_INVALID, "rt_render: width*height*pass_spp must be < 2^31");
+    const int total_passes = (ctx->ray_count + pass_spp - 1) / pass_spp;
+    const int pass_first = std::max(0, opts.pass_first);
+    const int pass_end = opts.pass_count > 0 ? std::min(total_passes, pass_first + opts.pass_count) : total_passes;
+    const bool collect = opts.collect_stats != 0;
+    const bool sort = opts.sort != 0 && ctx->bounces > 1;
+    int key_bits = opts.sort_bits > 0 ? opts.sort_bits : 15;  // 4 bits per axis + octant = two 8-bit digit passes
+    key_bits = std::min(30, std::max(6, key_bits));
+    key_bits = 3 + 3 * ((key_bits - 3) / 3);
+    // random.cuh:28: inc = 820957824423429, used as (inc | 1); other streams pick other odd increments
+    const unsigned long long pcg_inc = (820957824423429ULL + 2ULL * 0x9E3779B97F4A7C15ULL * (unsigned long long)std::max(0, opts.stream_id)) | 1ULL;
+
+    RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = ensure_framebuffer(ctx);
+    if (rc != RT_OK) return rc;
+    if ((rc = ensure_queues(ctx, pixels * (size_t)std::min(pass_spp, std::max(1, ctx->ray_count)), sort)) != RT_OK) return rc;
+
+    int blocks_per_sm = 0;
+    RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, bounce_kernel<false, false>, kBlock, 0));
+    const int grid = ctx->sm_count * std::max(1, blocks_per_sm);
+
+    RT_CUDA(ctx, cudaMemsetAsync(ctx->d_fb, 0, pixels * 3 * sizeof(float), ctx->stream));
+    RT_CUDA(ctx, cudaMemsetAsync(ctx->d_totals, 0, sizeof(RenderTotals), ctx->stream));
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
+
+    int launches = 0, passes_done = 0;
+    long long primaries = 0;
+    for (int pass = pass_first; pass < pass_end; pass++) {
+        const int before = ctx->ray_count - pass * pass_spp;
+        const int rays_to_cast = std::min(before, pass_spp);
+        const int remaining = before - rays_to_cast;  // the reference's `remaining_rays` after the decrement (:224-225)
+        const uint32_t total = (uint32_t)(pixels * (size_t)rays_to_cast);
+        primaries += total;
+        RT_CUDA(ctx, cudaMemsetAsync(ctx->d_pc, 0, sizeof(PassCounters), ctx->stream));
+        const uint32_t *order = nullptr;
+        for (int b = 0; b < ctx->bounces; b++) {
+            BounceArgs a{};
+            a.in = ctx->queue[(b + 1) & 1];
+            a.out = (b + 1 < ctx->bounces) ? ctx->queue[b & 1] : RayQueue{nullptr, nullptr, nullptr};
+            a.order = order;
+            a.keys_out = (sort && b + 1 < ctx->bounces) ? ctx->d_keys[0] : nullptr;
+            a.pc = ctx->d_pc;
+            a.totals = ctx->d_totals;
+            a.framebuffer = ctx->d_fb;
+            a.n_first = total;
+            a.bounce = b;
+            a.rays_per_pixel = rays_to_cast;
+            a.gen_seed = 709579u * (uint32_t)remaining;                                // scene.cu:81
+            a.proc_seed = 279220567u * (uint32_t)(remaining * 20 + b);                 // raytracing.cu:89,236
+            a.pcg_inc = pcg_inc;
+            a.key_bits = key_bits;
+            if (b == 0) launch_bounce<true>(collect, grid, ctx->stream, ctx->ds, a);
+            else launch_bounce<false>(collect, grid, ctx->stream, ctx->ds, a);
+            launches++;
+            order = nullptr;
+            if (a.keys_out) {
+                uint32_t *sk, *sv;
+                if ((rc = enqueue_sort(ctx, &ctx->d_pc->count[b + 1], total, key_bits, true, &sk, &sv, &launches)) != RT_OK) return rc;
+                order = sv;
+            }
+        }
+        passes_done++;
+    }
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
+    RT_CUDA(ctx, cudaGetLastError());
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        float ms = 0;
+        RT_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_start, ctx->ev_stop));
+        RenderTotals t;
+        RT_CUDA(ctx, cudaMemcpy(&t, ctx->d_totals, sizeof(t), cudaMemcpyDeviceToHost));
+        stats->loop_seconds = ms * 1e-3;
+        stats->primary_rays = primaries;
+        stats->live_ray_bounces = (int64_t)t.live_ray_bounces;
+        stats->internal_visits = (int64_t)t.internal_visits;
+        stats->triangle_tests = (int64_t)t.triangle_tests;
+        stats->kernel_launches = launches;
+        stats->passes = passes_done;
+        for (int b = 0; b < 32; b++) {
+            stats->live_per_bounce[b] = (int64_t)t.live_per_bounce[b];
+            if (sort && b >= 1) stats->sorted_pairs += (int64_t)t.live_per_bounce[b];
+        }
+        stats->total_seconds = std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - wall0).count();
+    }
+    return RT_OK;
+}
+
+}  // namespace
+
+extern "C" int rt_render_device(rt_ctx *ctx, const rt_render_opts *opts, float **out_dev, rt_stats *stats)
+{
+    int rc = render_impl(ctx, opts, stats);
+    if (rc == RT_OK && out_dev) *out_dev = ctx->d_fb;
+    return rc;
+}
+
+extern "C" int rt_render(rt_ctx *ctx, const rt_render_opts *opts, float *out_rgb_sum, rt_stats *stats)
+{
+    auto wall0 = std::chrono::high_resolution_clock::now();
+    if (!out_rgb_sum) return fail(ctx, RT_ERR_INVALID, "rt_render: null output buffer");
+    int rc = render_impl(ctx, opts, stats);
+    if (rc != RT_OK) return rc;
+    RT_CUDA(ctx, cudaMemcpyAsync(out_rgb_sum, ctx->d_fb, ctx->fb_pixels * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (stats) stats->total_seconds = std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - wall0).count();
+    return RT_OK;
+}
+
+extern "C" int rt_framebuffer_upload(rt_ctx *ctx, const float *rgb_sum)
+{
+    if (!ctx || !rgb_sum) return fail(ctx, RT_ERR_INVALID, "rt_framebuffer_upload: null argument");
+    if (!ctx->has_scene) return fail(ctx, RT_ERR_INVALID, "rt_framebuffer_upload: no scene uploaded");
+    RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = ensure_framebuffer(ctx);
+    if (rc != RT_OK) return rc;
+    RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_fb, rgb_sum, ctx->fb_pixels * 3 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+extern "C" int rt_postprocess(rt_ctx *ctx, int bloom, float *out_rgb_sum, uint8_t *out_rgb8)
+{
+    if (!ctx) return fail(nullptr, RT_ERR_INVALID, "rt_postprocess: null context");
+    if (!ctx->d_fb || !ctx->fb_pixels) return fail(ctx, RT_ERR_INVALID, "rt_postprocess: nothing rendered");
+    RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int w = ctx->ds.width, h = ctx->ds.height;
+    const size_t px = ctx->fb_pixels;
+    const int grid = (int)((px + 127) / 128);
+    if (bloom) {
+        const float threshold = (float)(0.7 * ctx->ray_count);  // raytracing.cu:376
+        bloom_h_kernel<<<grid, 128, 0, ctx->stream>>>(ctx->d_fb, ctx->d_fb_tmp, threshold, w, h);
+        bloom_v_add_kernel<<<grid, 128, 0, ctx->stream>>>(ctx->d_fb_tmp, ctx->d_fb, ctx->d_fb_tmp2, w, h);
+        std::swap(ctx->d_fb, ctx->d_fb_tmp2);
+    }
+    if (out_rgb_sum) RT_CUDA(ctx, cudaMemcpyAsync(out_rgb_sum, ctx->d_fb, px * 3 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_rgb8) {
+        const float scale = ctx->exposure / (float)ctx->ray_count;  // raytracing.cu:290
+        tonemap_kernel<<<(int)((px * 3 + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_fb, ctx->d_rgb8, scale, px * 3);
+        RT_CUDA(ctx, cudaMemcpyAsync(out_rgb8, ctx->d_rgb8, px * 3, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    RT_CUDA(ctx, cudaGetLastError());
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+// ---- kernel-level entry points (parity hooks) -------------------------------------------------------------------
+namespace {
+struct DeviceBuffer {  // scoped scratch allocation
+    void *p = nullptr;
+    ~DeviceBuffer() { if (p) cudaFree(p); }
+};
+int hook_grid(const rt_ctx *ctx, size_t n)
+{
+    return (int)std::min<size_t>((size_t)ctx->sm_count * kBlocksPerSM, std::max<size_t>(1, (n + kBlock - 1) / kBlock));
+}
+}  // namespace
+
+extern "C" int rt_trace_closest(rt_ctx *ctx, const float *rays6, int32_t n, int32_t with_spheres, int32_t *out_prim, float *out_t,
+                                rt_stats *stats)
+{
+    if (!ctx || !rays6 || !out_prim || !out_t || n < 0) return fail(ctx, RT_ERR_INVALID, "rt_trace_closest: bad argument");
+    if (!ctx->has_scene) return fail(ctx, RT_ERR_INVALID, "rt_trace_closest: no scene uploaded");
+    if (n == 0) return RT_OK;
+    RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    DeviceBuffer rays, prim, t;
+    RT_CUDA(ctx, cudaMalloc(&rays.p, (size_t)n * 6 * sizeof(float)));
+    RT_CUDA(ctx, cudaMalloc(&prim.p, (size_t)n * sizeof(int)));
+    RT_CUDA(ctx, cudaMalloc(&t.p, (size_t)n * sizeof(float)));
+    RT_CUDA(ctx, cudaMemcpyAsync(rays.p, rays6, (size_t)n * 6 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    RT_CUDA(ctx, cudaMemsetAsync(ctx->d_totals, 0, sizeof(RenderTotals), ctx->stream));
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
+    if (stats)
+        trace_kernel<true><<<hook_grid(ctx, n), kBlock, 0, ctx->stream>>>(ctx->ds, (const float *)rays.p, (uint32_t)n, with_spheres,
+                                                                         (int *)prim.p, (float *)t.p, ctx->d_totals);
+    else
+        trace_kernel<false><<<hook_grid(ctx, n), kBlock, 0, ctx->stream>>>(ctx->ds, (const float *)rays.p, (uint32_t)n, with_spheres,
+                                                                          (int *)prim.p, (float *)t.p, ctx->d_totals);
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
+    RT_CUDA(ctx, cudaGetLastError());
+    RT_CUDA(ctx, cudaMemcpyAsync(out_prim, prim.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA(ctx, cudaMemcpyAsync(out_t, t.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        std::memset(stats, 0, sizeof(*stats));
+        float ms = 0;
+        RT_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_start, ctx->ev_stop));
+        RenderTotals tot;
+        RT_CUDA(ctx, cudaMemcpy(&tot, ctx->d_totals, sizeof(tot), cudaMemcpyDeviceToHost));
+        stats->loop_seconds = ms * 1e-3;
+        stats->live_ray_bounces = n;
+        stats->internal_visits = (int64_t)tot.internal_visits;
+        stats->triangle_tests = (int64_t)tot.triangle_tests;
+        stats->kernel_launches = 1;
+    }
+    return RT_OK;
+}
+
+extern "C" int rt_generate_rays(rt_ctx *ctx, int32_t rays_per_pixel, int32_t first, int32_t n, int32_t seed, float *out12)
+{
+    if (!ctx || !out12 || n < 0 || rays_per_pixel <= 0 || first < 0) return fail(ctx, RT_ERR_INVALID, "rt_generate_rays: bad argument");
+    if (!ctx->has_scene) return fail(ctx, RT_ERR_INVALID, "rt_generate_rays: no scene uploaded");
+    if (n == 0) return RT_OK;
+    RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    DeviceBuffer out;
+    RT_CUDA(ctx, cudaMalloc(&out.p, (size_t)n * 12 * sizeof(float)));
+    RT_CUDA(ctx, cudaMemsetAsync(out.p, 0, (size_t)n * 12 * sizeof(float), ctx->stream));
+    generate_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->ds, rays_per_pixel, (uint32_t)first, (uint32_t)n, 709579u * (uint32_t)seed,
+                                                              820957824423429ULL | 1ULL, (float *)out.p);
+    RT_CUDA(ctx, cudaGetLastError());
+    RT_CUDA(ctx, cudaMemcpyAsync(out12, out.p, (size_t)n * 12 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+extern "C" int rt_process_rays(rt_ctx *ctx, float *ray_data12, const uint32_t *seeds, int32_t n)
+{
+    if (!ctx || !ray_data12 || !seeds || n < 0) return fail(ctx, RT_ERR_INVALID, "rt_process_rays: bad argument");
+    if (!ctx->has_scene) return fail(ctx, RT_ERR_INVALID, "rt_process_rays: no scene uploaded");
+    if (n == 0) return RT_OK;
+    RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    DeviceBuffer data, sd;
+    RT_CUDA(ctx, cudaMalloc(&data.p, (size_t)n * 12 * sizeof(float)));
+    RT_CUDA(ctx, cudaMalloc(&sd.p, (size_t)n * sizeof(uint32_t)));
+    RT_CUDA(ctx, cudaMemcpyAsync(data.p, ray_data12, (size_t)n * 12 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    RT_CUDA(ctx, cudaMemcpyAsync(sd.p, seeds, (size_t)n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    process_kernel<<<hook_grid(ctx, n), kBlock, 0, ctx->stream>>>(ctx->ds, (float *)data.p, (const uint32_t *)sd.p, (uint32_t)n,
+                                                                  820957824423429ULL | 1ULL);
+    RT_CUDA(ctx, cudaGetLastError());
+    RT_CUDA(ctx, cudaMemcpyAsync(ray_data12, data.p, (size_t)n * 12 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+extern "C" int rt_sort_pairs(rt_ctx *ctx, uint32_t *keys, uint32_t *values, int32_t n, int32_t bits)
+{
+    if (!ctx || !keys || !values || n < 0 || bits <= 0 || bits > 32) return fail(ctx, RT_ERR_INVALID, "rt_sort_pairs: bad argument");
+    if (n == 0) return RT_OK;
+    RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = RT_OK;
+    if ((size_t)n > ctx->sort_capacity) {  // allocate the sort buffers only (queues untouched)
+        for (int i = 0; i < 2; i++) { release(ctx->d_keys[i]); release(ctx->d_vals[i]); }
+        release(ctx->d_sort_scratch);
+        ctx->sort_capacity = 0;
+        for (int i = 0; i < 2; i++) {
+            RT_CUDA(ctx, cudaMalloc(&ctx->d_keys[i], (size_t)n * sizeof(uint32_t)));
+            RT_CUDA(ctx, cudaMalloc(&ctx->d_vals[i], (size_t)n * sizeof(uint32_t)));
+        }
+        size_t tiles = ((size_t)n + kSortTile - 1) / kSortTile;
+        ctx->sort_scratch_words = (size_t)kSortMaxPasses * 256 + 16 + (size_t)kSortMaxPasses * tiles * 256;
+        RT_CUDA(ctx, cudaMalloc(&ctx->d_sort_scratch, ctx->sort_scratch_words * sizeof(uint32_t)));
+        ctx->sort_capacity = (size_t)n;
+    }
+    DeviceBuffer count;
+    uint32_t n32 = (uint32_t)n;
+    RT_CUDA(ctx, cudaMalloc(&count.p, sizeof(uint32_t)));
+    RT_CUDA(ctx, cudaMemcpyAsync(count.p, &n32, sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_keys[0], keys, (size_t)n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_vals[0], values, (size_t)n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    uint32_t *sk = nullptr, *sv = nullptr;
+    if ((rc = enqueue_sort(ctx, (const uint32_t *)count.p, (size_t)n, bits, false, &sk, &sv, nullptr)) != RT_OK) return rc;
+    RT_CUDA(ctx, cudaMemcpyAsync(keys, sk, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA(ctx, cudaMemcpyAsync(values, sv, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}

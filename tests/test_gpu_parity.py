@@ -1,0 +1,244 @@
+"""GPU parity tests: every kernel of the render core against the CPU oracle, through the C ABI (ctypes).
+
+Tolerances (stated once, used below):
+  * integer / index / byte work (sort, bloom selection, tone-map bytes, primary-ray generation): bit-exact;
+  * closest hit: primitive id equal unless the two candidates' t agree within 1e-5 relative (tie), t within 1e-5 rel
+    (north_star's dumped-ray criterion);
+  * one shading step: per-record values within 2e-4 relative-to-scale on >= 99.5 % of records (device sinf/cosf/atanf
+    differ from glibc's by a few ulp, and FMA contraction shifts t by ulps; a ray that grazes an edge may take the
+    other branch);
+  * images at matched seeds: relative RMSE of the linear radiance sums <= 2 %, far below the Monte-Carlo noise of the
+    tested spp (the seeds are the reference's `no_sort` GPU stream, so almost every path is identical).
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+import pyoracle as po
+import cuda_raytracer_b200 as rt
+from util import (ALL_SCENES, closest_hit_mismatches, load, oracle_arrays, oracle_closest, oracle_render, scene_rays)
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def renderer():
+    r = rt.Renderer(0)
+    yield r
+    r.close()
+
+
+def _setup(renderer, name, w=64, h=48, spp=25, bounces=10, exposure=1.0, use_bvh=True):
+    scene = load(name, use_bvh).set_image(w, h, spp, bounces, exposure)
+    renderer.upload(scene)
+    return scene, oracle_arrays(scene)
+
+
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_generate_rays_bit_exact(renderer, name):
+    scene, A = _setup(renderer, name, 64, 48, 25, 10)
+    S = A.oracle_struct()
+    for rpp, seed, first, n in [(20, 5, 0, 64 * 48 * 20), (5, 0, 1000, 4096), (1, 980, 0, 64 * 48)]:
+        want = np.zeros((n, 12), np.float32)
+        po.port().oracle_generate(C.byref(S), want.reshape(-1), rpp, first, n, seed)
+        got = renderer.generate_rays(rpp, first, n, seed)
+        assert got.tobytes() == want.tobytes()
+
+
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_closest_hit_vs_oracle(renderer, name):
+    scene, A = _setup(renderer, name)
+    rays = scene_rays(A, 200_000, seed=7)
+    prim, t = renderer.trace_closest(rays, with_spheres=False, stats=True)
+    st = renderer.last_stats
+    for near_first in (1, 0):  # the core's visiting order, then the reference's
+        want_prim, want_t, ctr = oracle_closest(A, rays, near_first)
+        bad, ties = closest_hit_mismatches(prim, t, want_prim, want_t, 1e-5)
+        assert len(bad) == 0, f"{name}: {len(bad)} closest-hit mismatches, first ray {bad[:5]}"
+        assert ties <= 20, f"{name}: {ties} id flips inside the tie tolerance"
+        if near_first:  # traversal statistics agree with the oracle's near-first counters
+            assert abs(st.internal_visits - ctr.internal_visits) <= 1e-3 * max(1, ctr.internal_visits)
+            assert abs(st.triangle_tests - ctr.triangle_tests) <= 1e-3 * max(1, ctr.triangle_tests)
+
+
+@pytest.mark.parametrize("name", ["cornell", "teapot"])
+def test_closest_hit_no_bvh(renderer, name):
+    """`no_bvh`: one root leaf holding every triangle (Q12); the packer splits it into <= 15-triangle chunks."""
+    scene, A = _setup(renderer, name, use_bvh=False)
+    rays = scene_rays(A, 2_000 if name == "teapot" else 50_000, seed=11)
+    prim, t = renderer.trace_closest(rays)
+    want_prim, want_t, _ = oracle_closest(A, rays, 0)
+    bad, ties = closest_hit_mismatches(prim, t, want_prim, want_t, 1e-5)
+    assert len(bad) == 0 and ties <= 5
+
+
+def test_closest_hit_edge_cases(renderer):
+    scene, A = _setup(renderer, "cornell")
+    rays = np.array([
+        [-278, 273, -800, 0, 0, 1],          # straight down the axis
+        [-278, 273, 100, 0, 1, 0],           # axis-parallel: two direction components are exactly 0 (inf reciprocals)
+        [-278, 273, 100, 0, -1, 0],
+        [-278, 0.0, 100, 1, 0, 0],           # origin ON the floor plane, travelling in it
+        [-278, 273, 100, 1e-30, 1, 1e-30],   # denormal-ish components
+        [5000, 5000, 5000, 1, 0, 0],         # outside, pointing away
+        [-278, 273, 559.2 - 0.004, 0, 0, 1], # hit closer than the 0.005 epsilon must be rejected
+        [-278, 273, 559.2 - 0.006, 0, 0, 1], # just beyond the epsilon must be accepted
+    ], np.float32)
+    prim, t = renderer.trace_closest(rays)
+    want_prim, want_t, _ = oracle_closest(A, rays, 1)
+    bad, _ = closest_hit_mismatches(prim, t, want_prim, want_t, 1e-5)
+    assert len(bad) == 0
+    assert prim[5] == -1 and t[5] == np.float32(1e30)
+    assert prim[6] == -1 and prim[7] >= 0
+    p0, t0 = renderer.trace_closest(np.zeros((0, 6), np.float32))  # empty batch
+    assert len(p0) == 0 and len(t0) == 0
+
+
+def test_closest_hit_with_spheres(renderer):
+    scene, A = _setup(renderer, "cornell_plus")
+    S = A.oracle_struct()
+    n = 64 * 48 * 20
+    data = np.zeros((n, 12), np.float32)
+    po.port().oracle_generate(C.byref(S), data.reshape(-1), 20, 0, n, 0)
+    rays = np.ascontiguousarray(data[:, :6])
+    prim, t = renderer.trace_closest(rays, with_spheres=True)
+    assert (prim[(prim >= 0)] < len(A.spheres) + len(A.triangles)).all()
+    assert ((prim >= 0) & (prim < len(A.spheres))).sum() > 100  # both spheres are in view
+
+
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_process_step_vs_oracle(renderer, name):
+    """One Scene::process_ray step per record at bounce 0 and at a deeper, incoherent bounce."""
+    scene, A = _setup(renderer, name)
+    S = A.oracle_struct()
+    n = 64 * 48 * 20
+    data = np.zeros((n, 12), np.float32)
+    po.port().oracle_generate(C.byref(S), data.reshape(-1), 20, 0, n, 3)
+    for bounce in range(3):
+        seeds = (np.arange(n, dtype=np.uint64) * 4137874753 + 279220567 * (3 * 20 + bounce)).astype(np.uint32)
+        want = data.copy()
+        po.port().oracle_process(C.byref(S), want.reshape(-1), seeds, n)
+        got = renderer.process_rays(data, seeds)
+        scale = np.maximum(np.abs(want), 1.0)
+        rec_ok = (np.abs(got - want) <= 2e-4 * scale).all(axis=1) | ~np.isfinite(want).all(axis=1)
+        frac = rec_ok.mean()
+        assert frac >= 0.995, f"{name} bounce {bounce}: only {frac:.4%} of records within tolerance"
+        dead_w = (want[:, 6:9] == 0).all(axis=1)
+        dead_g = (got[:, 6:9] == 0).all(axis=1)
+        assert (dead_w != dead_g).mean() < 2e-3
+        data = want  # continue from the oracle's state so errors do not compound
+
+
+@pytest.mark.parametrize("name,w,h,spp,bounces", [
+    ("cornell", 64, 64, 40, 10), ("cornell_plus", 64, 64, 40, 10), ("spheres", 64, 64, 40, 10),
+    ("teapot", 64, 48, 25, 10), ("glass_teapot", 64, 48, 25, 10), ("lamp", 64, 48, 25, 10)])
+def test_image_vs_oracle_matched_seeds(renderer, name, w, h, spp, bounces):
+    scene, A = _setup(renderer, name, w, h, spp, bounces)
+    want, ctr = oracle_render(A, seed_mode=1)
+    for sort in (False, True):
+        got = renderer.render(sort=sort, collect_stats=True)
+        st = renderer.last_stats
+        rel = np.sqrt(np.mean((got - want) ** 2)) / max(1e-12, np.sqrt(np.mean(want ** 2)))
+        assert rel <= 0.02, f"{name} sort={sort}: relative RMSE {rel:.4f}"
+        assert abs(got.mean() - want.mean()) <= 2e-3 * max(1e-9, abs(want.mean()))
+        assert abs(st.live_ray_bounces - ctr.live_ray_bounces) <= 2e-3 * ctr.live_ray_bounces
+        assert st.primary_rays == w * h * spp
+        assert st.passes == (spp + 19) // 20
+
+
+def test_sort_on_off_same_image(renderer):
+    """Seeds follow the ray, not its slot: reordering must not change the image beyond float summation order."""
+    _setup(renderer, "lamp", 96, 64, 20, 10)
+    a = renderer.render(sort=False)
+    b = renderer.render(sort=True)
+    c = renderer.render(sort=True, sort_bits=24)
+    assert np.allclose(a, b, rtol=1e-4, atol=1e-4 * a.mean())
+    assert np.allclose(a, c, rtol=1e-4, atol=1e-4 * a.mean())
+
+
+def test_pass_split_sums_to_whole(renderer):
+    """The multi-GPU spp split: disjoint pass ranges add up to the full render."""
+    _setup(renderer, "cornell_plus", 64, 64, 70, 8)  # 4 passes: 20,20,20,10
+    whole = renderer.render(sort=True)
+    parts = [renderer.render(sort=True, pass_first=f, pass_count=c) for f, c in ((0, 1), (1, 2), (3, 1))]
+    assert np.allclose(sum(parts), whole, rtol=1e-4, atol=1e-4 * whole.mean())
+    assert renderer.last_stats.passes == 1
+
+
+def test_edge_configs(renderer):
+    _setup(renderer, "cornell", 33, 17, 1, 1)  # ragged size, one sample, one bounce: only emitters seen directly
+    img = renderer.render(sort=True)
+    assert img.shape == (17, 33, 3) and np.isfinite(img).all()
+    _setup(renderer, "cornell", 16, 16, 0, 4)  # zero samples -> black
+    assert not renderer.render().any()
+    _setup(renderer, "spheres", 40, 30, 21, 3)  # no triangles at all (empty root leaf, Q12), ragged last pass
+    img = renderer.render(sort=True)
+    assert np.isfinite(img).all() and img.mean() > 0
+
+
+@pytest.mark.parametrize("n,bits", [(0, 32), (1, 32), (31, 8), (4096, 16), (4097, 32), (1_000_003, 32), (300_000, 15), (70_000, 24)])
+def test_radix_sort_pairs(renderer, n, bits):
+    rs = np.random.RandomState(n + bits)
+    keys = rs.randint(0, 2 ** 32, size=n, dtype=np.uint64).astype(np.uint32)
+    if bits < 32:
+        keys &= np.uint32((1 << bits) - 1)
+    if n > 100:
+        keys[: n // 3] = keys[0]  # long runs of equal keys exercise stability
+    vals = np.arange(n, dtype=np.uint32)
+    k, v = renderer.sort_pairs(keys, vals, bits)
+    order = np.argsort(keys, kind="stable")
+    assert (k == keys[order]).all()
+    assert (v == vals[order]).all()
+
+
+def test_radix_sort_partial_bits_is_stable(renderer):
+    """Sorting on the low 8 bits only must leave the high bits in input order within each bucket."""
+    rs = np.random.RandomState(5)
+    keys = rs.randint(0, 2 ** 32, size=50_000, dtype=np.uint64).astype(np.uint32)
+    vals = rs.randint(0, 2 ** 32, size=50_000, dtype=np.uint64).astype(np.uint32)
+    k, v = renderer.sort_pairs(keys, vals, 8)
+    order = np.argsort(keys & 0xFF, kind="stable")
+    assert (k == keys[order]).all() and (v == vals[order]).all()
+
+
+def test_bloom_and_tonemap_bit_exact(renderer):
+    scene, A = _setup(renderer, "cornell", 80, 60, 20, 4, exposure=1.0)
+    rs = np.random.RandomState(3)
+    img = (rs.rand(60, 80, 3).astype(np.float32) ** 4) * 40.0  # some pixels above the 0.7*ray_count threshold
+    img[10:14, 20:30] = 500.0
+    img[0, 0] = 1000.0    # corner: edge-clamped tap counts
+    img[59, 79] = 900.0
+    want = img.copy()
+    po.port().oracle_bloom(want.reshape(-1), 80, 60, 20)
+    want8 = np.zeros((60, 80, 3), np.uint8)
+    po.port().oracle_tonemap(want.reshape(-1), 80 * 60, 1.0, 20, want8.reshape(-1))
+    renderer.framebuffer_upload(img)
+    got, got8 = renderer.postprocess(bloom=True, want_sum=True, want_rgb8=True)
+    assert got.tobytes() == want.tobytes()
+    assert got8.tobytes() == want8.tobytes()
+    renderer.framebuffer_upload(img)  # tone map alone
+    _, plain8 = renderer.postprocess(bloom=False)
+    ref8 = np.zeros((60, 80, 3), np.uint8)
+    po.port().oracle_tonemap(img.reshape(-1), 80 * 60, 1.0, 20, ref8.reshape(-1))
+    assert plain8.tobytes() == ref8.tobytes()
+
+
+@pytest.mark.parametrize("name", ["cornell", "teapot", "lamp"])
+def test_closest_hit_vs_reference_kernel(renderer, name):
+    """north_star's first criterion: the reference's own device code (compiled in place into oracle/_ref, fast-math as
+    its author builds it) run on this GPU over a dumped ray batch."""
+    L = po.shim()
+    if L is None:
+        pytest.skip("oracle/_ref/libref_shim.so was not built (needs /root/reference at build time)")
+    from util import SCENES
+    ref = po.RefScene(name + ".scene", cwd=SCENES)
+    scene, A = _setup(renderer, name)
+    rays = scene_rays(A, 200_000, seed=21)
+    t_ref = np.zeros(len(rays), np.float32)
+    i_ref = np.zeros(len(rays), np.int32)
+    assert L.ref_closest_hit_gpu(ref.handle, rays, len(rays), t_ref, i_ref) == 0
+    prim, t = renderer.trace_closest(rays)
+    bad, ties = closest_hit_mismatches(prim, t, i_ref, t_ref, 1e-5)
+    assert len(bad) <= 2, f"{len(bad)} mismatches vs the reference kernel"  # fast-math reciprocals on the reference side
+    assert ties <= 20

@@ -1,0 +1,80 @@
+"""Shared helpers of the test-suite: scene loading through the product's host layer, oracle plumbing, comparisons."""
+import ctypes as C
+import os
+
+import numpy as np
+
+import pyoracle as po
+import cuda_raytracer_b200 as rt
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SCENES = os.path.join(ROOT, "scenes")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+ALL_SCENES = ["cornell", "cornell_plus", "spheres", "teapot", "glass_teapot", "lamp"]
+
+_scene_cache = {}
+
+
+def load(name, use_bvh=True):
+    """Product host loader (cached per (name, use_bvh)); the image block is reset by the caller with set_image."""
+    key = (name, use_bvh)
+    if key not in _scene_cache:
+        _scene_cache[key] = rt.load_scene(name + ".scene", use_bvh=use_bvh, cwd=SCENES)
+    return _scene_cache[key]
+
+
+def oracle_arrays(scene):
+    """pyoracle.SceneArrays built from the product loader's arrays (which tests/test_host_scene.py pins to the reference)."""
+    a = scene.arrays()
+    floats = {k: a[k] for k in ("camera_position", "forward", "up", "vertical_fov", "exposure", "min_coord", "inv_dimensions",
+                                "scaled_right", "scaled_up", "near_plane_top_left", "inv_width", "inv_height")}
+    return po.SceneArrays(a["spheres"], a["triangles"], a["material_indices"], a["materials"], a["bvh"], a["env"],
+                          a["env_w"], a["env_h"], (a["width"], a["height"], a["ray_count"], a["bounces"]), floats)
+
+
+def scene_rays(arrays, n, seed):
+    """n seeded rays: origins uniform in the (slightly inflated) scene box, directions uniform on the sphere."""
+    rs = np.random.RandomState(seed)
+    if len(arrays.triangles):
+        lo, hi = arrays.bvh[0]["min"].astype(np.float64), arrays.bvh[0]["max"].astype(np.float64)
+    else:
+        lo, hi = np.full(3, -8.0), np.full(3, 8.0)
+    ext = hi - lo
+    o = lo - 0.1 * ext + 1.2 * ext * rs.rand(n, 3)
+    d = rs.randn(n, 3)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    return np.ascontiguousarray(np.concatenate([o, d], 1), np.float32)
+
+
+def oracle_closest(arrays, rays, near_first):
+    S = arrays.oracle_struct()
+    n = len(rays)
+    t = np.zeros(n, np.float32)
+    idx = np.zeros(n, np.int32)
+    c = po.Counters()
+    po.port().oracle_closest_hit(C.byref(S), rays, n, 1 if near_first else 0, t, idx, C.byref(c))
+    return idx, t, c
+
+
+def oracle_render(arrays, seed_mode=1, pass_first=0, pass_count=-1):
+    S = arrays.oracle_struct()
+    img = np.zeros((arrays.height, arrays.width, 3), np.float32)
+    c = po.Counters()
+    po.port().oracle_render(C.byref(S), seed_mode, pass_first, pass_count, img.reshape(-1), C.byref(c))
+    return img, c
+
+
+def closest_hit_mismatches(prim_a, t_a, prim_b, t_b, rel=1e-5):
+    """Indices where two closest-hit answers disagree beyond the stated tolerance: primitive ids must be equal unless
+    the two hit distances are within `rel` (a tie between adjacent primitives); t within `rel` relative."""
+    t_close = np.abs(t_a.astype(np.float64) - t_b.astype(np.float64)) <= rel * np.maximum(np.abs(t_a), np.abs(t_b)).astype(np.float64)
+    both_miss = (prim_a < 0) & (prim_b < 0)
+    ok = both_miss | t_close
+    return np.nonzero(~ok)[0], int(((prim_a != prim_b) & ok & ~both_miss).sum())
+
+
+def tonemap8(img_sum, exposure, ray_count):
+    out = np.zeros(img_sum.shape, np.uint8)
+    po.port().oracle_tonemap(np.ascontiguousarray(img_sum, np.float32).reshape(-1), img_sum.shape[0] * img_sum.shape[1],
+                             float(exposure), int(ray_count), out.reshape(-1))
+    return out
