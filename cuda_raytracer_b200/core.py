@@ -233,23 +233,26 @@ class Renderer:
         return self
 
     @staticmethod
-    def _opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits):
-        return RenderOpts(1 if sort else 0, pass_spp, pass_first, pass_count, 1 if collect_stats else 0, stream_id, sort_bits, 0)
+    def _opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing=False):
+        return RenderOpts(1 if sort else 0, pass_spp, pass_first, pass_count, 1 if collect_stats else 0, stream_id, sort_bits,
+                          1 if timing else 0)
 
-    def render(self, sort=True, out=None, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0):
+    def render(self, sort=True, out=None, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0,
+               timing=False):
         """rt_render: host output (float32[H,W,3] un-normalised sums). ``out`` may be a preallocated (pinned) array."""
         if out is None:
             out = np.empty((self.height, self.width, 3), np.float32)
         assert out.dtype == np.float32 and out.size == self.width * self.height * 3 and out.flags.c_contiguous
-        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits)
+        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing)
         st = Stats()
         _check(lib().rt_render(self._ctx, C.byref(o), out.ctypes.data, C.byref(st)), self._ctx)
         self.last_stats = st
         return out
 
-    def render_device(self, sort=True, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0):
+    def render_device(self, sort=True, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0,
+                      timing=False):
         """rt_render_device: returns the device pointer (int) of the float32[H*W*3] framebuffer."""
-        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits)
+        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing)
         st = Stats()
         ptr = C.c_void_p()
         _check(lib().rt_render_device(self._ctx, C.byref(o), C.byref(ptr), C.byref(st)), self._ctx)

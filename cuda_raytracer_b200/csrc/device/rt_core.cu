@@ -48,6 +48,7 @@ struct rt_ctx {
     PassCounters *d_pc = nullptr;
     RenderTotals *d_totals = nullptr;
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    std::vector<cudaEvent_t> ev_pool;  // per-launch timing (rt_render_opts.reserved & 1)
 };
 
 namespace {
@@ -235,6 +236,7 @@ extern "C" void rt_destroy(rt_ctx *ctx)
         release(ctx->d_keys[i]); release(ctx->d_vals[i]);
     }
     release(ctx->d_sort_scratch); release(ctx->d_pc); release(ctx->d_totals);
+    for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
     if (ctx->ev_stop) cudaEventDestroy(ctx->ev_stop);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -436,6 +438,19 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     const int pass_first = std::max(0, opts.pass_first);
     const int pass_end = opts.pass_count > 0 ? std::min(total_passes, pass_first + opts.pass_count) : total_passes;
     const bool collect = opts.collect_stats != 0;
+    const bool timing = (opts.reserved & 1) != 0;  // CUDA-event pair around every bounce kernel and every reorder pass
+    std::vector<int> ev_kind;                       // 0 = bounce kernel, 1 = reorder
+    auto mark = [&](int kind) -> int {
+        if (!timing) return RT_OK;
+        size_t k = ev_kind.size();
+        while (ctx->ev_pool.size() <= k) {
+            cudaEvent_t e;
+            if (cudaEventCreate(&e) != cudaSuccess) return RT_ERR_CUDA;
+            ctx->ev_pool.push_back(e);
+        }
+        ev_kind.push_back(kind);
+        return cudaEventRecord(ctx->ev_pool[k], ctx->stream) == cudaSuccess ? RT_OK : RT_ERR_CUDA;
+    };
     const bool sort = opts.sort != 0 && ctx->bounces > 1;
     int key_bits = opts.sort_bits > 0 ? opts.sort_bits : 15;  // 4 bits per axis + octant = two 8-bit digit passes
     key_bits = std::min(30, std::max(6, key_bits));
@@ -482,13 +497,17 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             a.proc_seed = 279220567u * (uint32_t)(remaining * 20 + b);                 // raytracing.cu:89,236
             a.pcg_inc = pcg_inc;
             a.key_bits = key_bits;
+            if ((rc = mark(0)) != RT_OK) return fail(ctx, rc, "event record failed");
             if (b == 0) launch_bounce<true>(collect, grid, ctx->stream, ctx->ds, a);
             else launch_bounce<false>(collect, grid, ctx->stream, ctx->ds, a);
+            if ((rc = mark(0)) != RT_OK) return fail(ctx, rc, "event record failed");
             launches++;
             order = nullptr;
             if (a.keys_out) {
                 uint32_t *sk, *sv;
+                if ((rc = mark(1)) != RT_OK) return fail(ctx, rc, "event record failed");
                 if ((rc = enqueue_sort(ctx, &ctx->d_pc->count[b + 1], total, key_bits, true, &sk, &sv, &launches)) != RT_OK) return rc;
+                if ((rc = mark(1)) != RT_OK) return fail(ctx, rc, "event record failed");
                 order = sv;
             }
         }
@@ -514,6 +533,11 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         for (int b = 0; b < 32; b++) {
             stats->live_per_bounce[b] = (int64_t)t.live_per_bounce[b];
             if (sort && b >= 1) stats->sorted_pairs += (int64_t)t.live_per_bounce[b];
+        }
+        for (size_t k = 0; k + 1 < ev_kind.size(); k += 2) {
+            float e_ms = 0;
+            RT_CUDA(ctx, cudaEventElapsedTime(&e_ms, ctx->ev_pool[k], ctx->ev_pool[k + 1]));
+            (ev_kind[k] == 0 ? stats->trace_shade_ms : stats->sort_ms) += e_ms;
         }
         stats->total_seconds = std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - wall0).count();
     }

@@ -75,7 +75,7 @@ typedef struct rt_render_opts {
                               k > 0 = disjoint PCG streams: stream k's `inc` differs (random.cuh:28), for multi-GPU runs
                               that do NOT want pass-identical images */
     int32_t sort_bits;     /* key width for the reorder pass, 0 = default */
-    int32_t reserved;
+    int32_t reserved;      /* bit 0: time every bounce kernel / reorder pass with CUDA events (rt_stats.trace_shade_ms, sort_ms) */
 } rt_render_opts;
 
 typedef struct rt_stats {
@@ -88,7 +88,7 @@ typedef struct rt_stats {
     int64_t sorted_pairs;       /* (key,index) pairs pushed through the reorder pass */
     int32_t kernel_launches;    /* kernels of THIS library launched inside the loop */
     int32_t passes;
-    double trace_shade_ms;      /* CUDA-event sum over the bounce kernels (0 unless collect_stats or RT_TIMING=1) */
+    double trace_shade_ms;      /* CUDA-event sum over the bounce kernels (0 unless rt_render_opts.reserved bit 0) */
     double sort_ms;
     int64_t live_per_bounce[32];
 } rt_stats;

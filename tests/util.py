@@ -64,10 +64,20 @@ def oracle_render(arrays, seed_mode=1, pass_first=0, pass_count=-1):
     return img, c
 
 
-def closest_hit_mismatches(prim_a, t_a, prim_b, t_b, rel=1e-5):
+def scene_diag(arrays):
+    """Diagonal of the triangle root box (1.0 when there are no triangles)."""
+    if not len(arrays.triangles):
+        return 1.0
+    return float(np.linalg.norm(arrays.bvh[0]["max"].astype(np.float64) - arrays.bvh[0]["min"].astype(np.float64)))
+
+
+def closest_hit_mismatches(prim_a, t_a, prim_b, t_b, rel=1e-5, abs_tol=0.0):
     """Indices where two closest-hit answers disagree beyond the stated tolerance: primitive ids must be equal unless
-    the two hit distances are within `rel` (a tie between adjacent primitives); t within `rel` relative."""
-    t_close = np.abs(t_a.astype(np.float64) - t_b.astype(np.float64)) <= rel * np.maximum(np.abs(t_a), np.abs(t_b)).astype(np.float64)
+    the two hit distances are within tolerance (a tie between adjacent primitives); t within `rel` relative
+    (+ `abs_tol`, used only against the un-contracted CPU arithmetic: Moller-Trumbore subtracts scene-sized coordinates,
+    so an FMA-contracting build moves a tiny t by ~ulp(scene size), not ulp(t))."""
+    diff = np.abs(t_a.astype(np.float64) - t_b.astype(np.float64))
+    t_close = diff <= rel * np.maximum(np.abs(t_a), np.abs(t_b)).astype(np.float64) + abs_tol
     both_miss = (prim_a < 0) & (prim_b < 0)
     ok = both_miss | t_close
     return np.nonzero(~ok)[0], int(((prim_a != prim_b) & ok & ~both_miss).sum())
