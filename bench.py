@@ -1,0 +1,395 @@
+#!/usr/bin/env python3
+"""bench.py — headline metric of the render path: Mrays/s (all bounces) on lamp.scene, ms/frame.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload lamp_4k|lamp_1k|...] [--impl reference]
+  torchrun ... bench.py --gpus N ...        (one rank per GPU, NCCL; launched by the driver for N > 1)
+
+A "step" is one whole frame of the workload: every pass of every bounce (generate -> closest hit -> shade -> compact
+[-> reorder]) plus, for N > 1, the NCCL reduce of the float accumulation buffer to rank 0. The frame's passes are split
+across the ranks (strong scaling: the frame is fixed). `value` = live ray-bounces of the whole frame /
+device time (CUDA events on the render stream, max over ranks). `e2e` is the same frame through the reference-facing
+call with HOST buffers: rt_scene_upload (BVH packing + H2D) + render + D2H of the sums, every step.
+
+Only the `cpu_baseline` leg and `--impl reference` execute anything under oracle/ (the reference's own CPU path).
+"""
+import argparse
+import json
+import os
+import re
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+SCENES = os.path.join(ROOT, "scenes")
+REF_BIN = os.path.join(ROOT, "oracle", "_ref", "raytracing_ref")
+
+# name -> (scene, width, height, spp, bounces)   BASELINE.md §3 configs
+WORKLOADS = {
+    "lamp_4k": ("lamp", 3840, 2160, 640, 10),      # BASELINE.json configs[4]: "lamp.scene at 4K and high rays_per_pixel"
+    "lamp_1k": ("lamp", 1000, 1000, 1000, 10),     # lamp.scene as shipped
+    "teapot_1k": ("teapot", 1000, 1000, 1000, 10),
+    "cornell_1k": ("cornell", 1000, 1000, 1000, 10),
+    "cornell_plus_1k": ("cornell_plus", 1000, 1000, 1000, 10),
+    "spheres_1k": ("spheres", 1000, 1000, 1000, 10),
+    "glass_teapot_1k": ("glass_teapot", 1000, 1000, 1000, 10),
+}
+METRIC = "Mrays/s (all bounces) on lamp.scene; ms/frame"
+PASS_SPP = 20  # MAX_RAYS_PER_PIXEL_PER_PASS, raytracing.cu:109
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=3)
+    p.add_argument("--warmup", type=int, default=3)
+    p.add_argument("--workload", default="lamp_4k", choices=sorted(WORKLOADS))
+    p.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    p.add_argument("--sort", type=int, default=0, help="1 = reorder live rays between bounces")
+    p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-ref-gpu", action="store_true", help="skip timing the reference's sm_100a GPU binary")
+    return p.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu_index, self.rows, self.proc = str(gpu_index), [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) >= 8 and f[0] == self.gpu_index:
+                self.rows.append(f)
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = sorted(float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(r[4 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None,
+                "sm_max_mhz": max((float(r[2]) for r in self.rows if r[2].replace(".", "").isdigit()), default=None),
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def visible_gpu_index(local_rank):
+    vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+    if vis:
+        parts = [v for v in vis.split(",") if v.strip() != ""]
+        if local_rank < len(parts) and parts[local_rank].strip().isdigit():
+            return int(parts[local_rank])
+    return local_rank
+
+
+def pass_range(total_passes, rank, world):
+    """Contiguous block of passes for `rank` (passes are the independent unit, raytracing.cu:222-254)."""
+    base, extra = divmod(total_passes, world)
+    first = rank * base + min(rank, extra)
+    return first, base + (1 if rank < extra else 0)
+
+
+# ---- reference arm / cpu_baseline: the reference's own CPU path (oracle/_ref/raytracing_ref cpu no_gpu) -------------
+def _scene_file_with_image(scene, w, h, spp, bounces):
+    src = open(os.path.join(SCENES, scene + ".scene")).read()
+    exposure = re.search(r"(?m)^image\s+\S+\s+\S+\s+\S+\s+\S+\s+(\S+)", src)
+    line = f"image {w} {h} {spp} {bounces} {exposure.group(1) if exposure else 1}"
+    f = tempfile.NamedTemporaryFile("w", suffix=".scene", delete=False)
+    f.write(re.sub(r"(?m)^image .*$", line, src))
+    f.close()
+    return f.name
+
+
+def live_per_primary(scene, w, h, bounces):
+    """Live ray-bounces per primary ray, counted by the oracle port on a 1/8-scale image of the same camera (CPU seeds).
+    The reference binary prints no counts; the ratio converts its `CPU Took` time into the metric's unit."""
+    import ctypes as C
+
+    import numpy as np
+
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pyoracle as po
+
+    import cuda_raytracer_b200 as rt
+    s = rt.load_scene(scene + ".scene", cwd=SCENES).set_image(max(16, w // 8), max(16, h // 8), 20, bounces)
+    a = s.arrays()
+    floats = {k: a[k] for k in ("camera_position", "forward", "up", "vertical_fov", "exposure", "min_coord", "inv_dimensions",
+                                "scaled_right", "scaled_up", "near_plane_top_left", "inv_width", "inv_height")}
+    arrays = po.SceneArrays(a["spheres"], a["triangles"], a["material_indices"], a["materials"], a["bvh"], a["env"], a["env_w"],
+                            a["env_h"], (a["width"], a["height"], a["ray_count"], a["bounces"]), floats)
+    S = arrays.oracle_struct()
+    img = np.zeros(a["width"] * a["height"] * 3, np.float32)
+    c = po.Counters()
+    po.port().oracle_render(C.byref(S), 0, 0, -1, img, C.byref(c))
+    return c.live_ray_bounces / float(a["width"] * a["height"] * 20), po.port().oracle_max_threads()
+
+
+def run_reference_cpu(scene, w, h, spp, bounces):
+    """One run of the reference program's CPU path; returns seconds from its own `CPU Took` line."""
+    path = _scene_file_with_image(scene, w, h, spp, bounces)
+    try:
+        out = subprocess.run([REF_BIN, path, "cpu", "no_gpu"], cwd=SCENES, capture_output=True, text=True, timeout=1800).stdout
+    finally:
+        os.unlink(path)
+    m = re.search(r"CPU Took ([0-9.eE+-]+)s", out)
+    if not m:
+        raise RuntimeError("reference CPU run printed no `CPU Took` line: " + out[-400:])
+    return float(m.group(1))
+
+
+def size_cpu_sample(scene, w, h, bounces, target_seconds=12.0):
+    """Pick the sample: full resolution, spp chosen so one run takes about target_seconds (1..20 spp = at most one pass)."""
+    cw, ch = max(64, w // 4), max(64, h // 4)
+    t = run_reference_cpu(scene, cw, ch, 4, bounces)
+    primaries_per_s = cw * ch * 4 / max(t, 1e-6)
+    spp = int(max(1, min(PASS_SPP, target_seconds * primaries_per_s / (w * h))))
+    return spp
+
+
+def reference_arm(args, rank, world):
+    if rank != 0:
+        return 0
+    scene, w, h, spp, bounces = WORKLOADS[args.workload]
+    cfg = {"workload": f"{scene}.scene {w}x{h} {spp} spp {bounces} bounces (lamp-subset geometry, synthetic env map)", "l2": "n/a (CPU)"}
+    if not os.path.exists(REF_BIN):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/raytracing_ref was not built (needs /root/reference at build time)"}))
+        return 0
+    ratio, threads = live_per_primary(scene, w, h, bounces)
+    s_spp = size_cpu_sample(scene, w, h, bounces, 10.0)
+    times = []
+    for i in range(args.warmup + args.steps):
+        t = run_reference_cpu(scene, w, h, s_spp, bounces)
+        if i >= args.warmup:
+            times.append(t)
+    sec = sum(times) / len(times)
+    live = ratio * w * h * s_spp
+    value = live / sec * 1e-6
+    sample = f"{w}x{h} x {s_spp} spp (one pass of the workload's {spp} spp), `raytracing_ref <scene> cpu no_gpu`, OpenMP {threads} threads"
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": cfg,
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "reference", "sample": sample},
+            "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+# ---- the B200 arm ------------------------------------------------------------------------------------------------------
+class _DevBuf:
+    """Zero-copy view of the core's device framebuffer for torch (so NCCL can reduce it in place)."""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
+
+
+def ref_gpu_timing(scene, w, h, bounces):
+    """The reference's sm_100a GPU build on the same box: `GPU Took` at two spp values -> steady-state slope."""
+    out = {}
+    for spp in (100, 300):
+        path = _scene_file_with_image(scene, w, h, spp, bounces)
+        try:
+            res = {}
+            for flags in ((), ("no_sort",)):
+                o = subprocess.run([REF_BIN, path, *flags], cwd=SCENES, capture_output=True, text=True, timeout=1800).stdout
+                m = re.search(r"GPU Took ([0-9.eE+-]+)s", o)
+                res["no_sort" if flags else "sort"] = float(m.group(1)) if m else None
+            out[spp] = res
+        finally:
+            os.unlink(path)
+    return out
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+
+    import numpy as np
+    import torch
+
+    import cuda_raytracer_b200 as rt
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the render core has no CPU fallback (use --impl reference for the CPU path)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    scene_name, w, h, spp, bounces = WORKLOADS[args.workload]
+    scene = rt.load_scene(scene_name + ".scene", cwd=SCENES).set_image(w, h, spp, bounces)
+    total_passes = (spp + PASS_SPP - 1) // PASS_SPP
+    first, count = pass_range(total_passes, rank, world)
+    sort = bool(args.sort)
+
+    r = rt.Renderer(local_rank)
+    r.upload(scene)
+    n_floats = w * h * 3
+    host_out = torch.empty(n_floats, dtype=torch.float32).pin_memory().numpy()
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def frame(timing=False):
+        """One step, inputs resident: this rank's passes, then the reduce of the accumulation buffer to rank 0."""
+        if count > 0:
+            ptr = r.render_device(sort=sort, pass_first=first, pass_count=count, timing=timing)
+            st = r.last_stats
+            dev_s, live, launches, tr_ms, so_ms = st.loop_seconds, st.live_ray_bounces, st.kernel_launches, st.trace_shade_ms, st.sort_ms
+        else:  # more ranks than passes: contribute zeros
+            ptr = r.render_device(sort=sort, pass_first=0, pass_count=1)
+            dev_s = live = launches = tr_ms = so_ms = 0
+        red_s = 0.0
+        if dist is not None:
+            fb = torch.as_tensor(_DevBuf(ptr, n_floats), device=f"cuda:{local_rank}")
+            if count == 0:
+                fb.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)
+            e1.record()
+            e1.synchronize()
+            red_s = e0.elapsed_time(e1) * 1e-3
+        return dev_s + red_s, live, launches, tr_ms, so_ms, red_s
+
+    def frame_e2e():
+        """The reference-facing call with host buffers: upload (BVH packing + H2D), render, D2H of the sums."""
+        t0 = time.perf_counter()
+        r.upload(scene)
+        if dist is None:
+            r.render(sort=sort, out=host_out.reshape(h, w, 3))
+        else:
+            ptr = r.render_device(sort=sort, pass_first=first, pass_count=max(count, 1))
+            fb = torch.as_tensor(_DevBuf(ptr, n_floats), device=f"cuda:{local_rank}")
+            if count == 0:
+                fb.zero_()
+            dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                torch.from_numpy(host_out).copy_(fb, non_blocking=False)
+            torch.cuda.synchronize()
+        return time.perf_counter() - t0
+
+    # stats-mode render of one pass: N_int / N_tri per live ray-bounce for the roofline's algorithmic bytes
+    r.render_device(sort=sort, pass_first=0, pass_count=1, collect_stats=True)
+    s1 = r.last_stats
+    n_int = s1.internal_visits / max(1, s1.live_ray_bounces)
+    n_tri = s1.triangle_tests / max(1, s1.live_ray_bounces)
+    bytes_per_unit = 104.0 + 64.0 * n_int + 48.0 * n_tri
+
+    for _ in range(args.warmup):
+        frame()
+    sampler = ClockSampler(visible_gpu_index(local_rank))
+    barrier()
+    sampler.start()
+    wall0 = time.perf_counter()
+    per_step = [frame(timing=True) for _ in range(args.steps)]
+    barrier()
+    wall = time.perf_counter() - wall0
+    clocks = sampler.stop()
+
+    dev_s = sum(p[0] for p in per_step)
+    live = sum(p[1] for p in per_step)
+    launches = sum(p[2] for p in per_step)
+    tr_ms = sum(p[3] for p in per_step)
+    so_ms = sum(p[4] for p in per_step)
+    red_s = sum(p[5] for p in per_step)
+
+    # e2e: warm once, then time K steps (wall clock around the public call, barrier + sync on both sides)
+    frame_e2e()
+    barrier()
+    e2e_t = [frame_e2e() for _ in range(args.steps)]
+    barrier()
+    e2e_s = sum(e2e_t)
+
+    if dist is not None:
+        t = torch.tensor([dev_s, e2e_s, tr_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_s, e2e_s, tr_ms_max = (float(v) for v in t)
+        t = torch.tensor([float(live), float(launches)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        live, launches = (float(v) for v in t)
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return 0
+
+    a = scene.desc()
+    scene_bytes = (a.sphere_count * 16 + a.triangle_count * 48 + (a.sphere_count + a.triangle_count) * 2 + a.material_count * 48 +
+                   (a.bvh_node_count // 2 + 1) * 64 + a.env_width * a.env_height * 16)
+    value = live / dev_s * 1e-6
+    e2e_value = live / e2e_s * 1e-6
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    # dominant kernel = bounce_kernel: algorithmic bytes of rank 0's launches / their summed CUDA-event durations
+    live_rank0 = sum(p[1] for p in per_step)
+    achieved = live_rank0 * bytes_per_unit / max(1e-9, tr_ms * 1e-3) * 1e-9
+    line = {
+        "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{scene_name}.scene {w}x{h} {spp} spp {bounces} bounces (lamp-subset geometry, synthetic env map)",
+                   "passes": total_passes, "pass_spp": PASS_SPP, "sort": int(sort), "parallelism": f"spp-split x{world} + NCCL reduce",
+                   "l2": "inputs larger than L2: ray queues are %.1f GB per pass; the packed scene (%.0f MB) is L2-resident by nature"
+                         % (w * h * PASS_SPP * 40 * 2 / 1e9, scene_bytes / 1e6)},
+        "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_s / args.steps * 1e3,
+                "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(n_floats * 4)},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "kernel": "bounce_kernel", "bytes_per_ray_bounce": bytes_per_unit, "n_int": n_int, "n_tri": n_tri,
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
+                     "kernel_share_of_step": tr_ms * 1e-3 / max(1e-9, sum(p[0] for p in per_step))},
+        "breakdown_ms_per_step": {"bounce_kernels": tr_ms / args.steps, "reorder": so_ms / args.steps, "nccl_reduce": red_s / args.steps * 1e3,
+                                  "wall": wall / args.steps * 1e3},
+    }
+    if world == 1 and not args.no_cpu_baseline and os.path.exists(REF_BIN):
+        ratio, threads = live_per_primary(scene_name, w, h, bounces)
+        s_spp = size_cpu_sample(scene_name, w, h, bounces, 12.0)
+        sec = run_reference_cpu(scene_name, w, h, s_spp, bounces)
+        line["cpu_baseline"] = {"value": ratio * w * h * s_spp / sec * 1e-6, "unit": "Mrays/s", "cores": threads, "kind": "reference",
+                                "sample": f"{w}x{h} x {s_spp} spp of the workload, raytracing_ref cpu no_gpu, {sec:.2f} s"}
+    if world == 1 and not args.no_ref_gpu and os.path.exists(REF_BIN):
+        rw, rh = (w, h) if w * h <= 1_000_000 else (1000, 1000)
+        tg = ref_gpu_timing(scene_name, rw, rh, bounces)
+        lpp = live / args.steps / (w * h * spp)
+        ref = {"config": f"{scene_name}.scene {rw}x{rh}, GPU Took at 100 and 300 spp", "gpu_took_s": tg}
+        for mode in ("sort", "no_sort"):
+            if tg[100].get(mode) and tg[300].get(mode):
+                slope = (tg[300][mode] - tg[100][mode]) / 200.0
+                ref[f"{mode}_mrays_per_s_steady"] = lpp * rw * rh / max(slope, 1e-9) * 1e-6
+        line["reference_gpu_sm100a"] = ref
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
