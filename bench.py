@@ -202,7 +202,8 @@ class _DevBuf:
 def ref_gpu_timing(scene, w, h, bounces):
     """The reference's sm_100a GPU build on the same box: `GPU Took` at two spp values -> steady-state slope."""
     out = {}
-    for spp in (100, 300):
+    lo, hi = (100, 300) if w * h <= 1_000_000 else (40, 120)  # whole passes of 20 spp; a few seconds in total
+    for spp in (lo, hi):
         path = _scene_file_with_image(scene, w, h, spp, bounces)
         try:
             res = {}
@@ -258,10 +259,10 @@ def main():
         if count > 0:
             ptr = r.render_device(sort=sort, pass_first=first, pass_count=count, timing=timing)
             st = r.last_stats
-            dev_s, live, launches, tr_ms, so_ms = st.loop_seconds, st.live_ray_bounces, st.kernel_launches, st.trace_shade_ms, st.sort_ms
+            dev_s, live, launches, tr_ms, sh_ms, so_ms = st.loop_seconds, st.live_ray_bounces, st.kernel_launches, st.trace_ms, st.shade_ms, st.sort_ms
         else:  # more ranks than passes: contribute zeros
             ptr = r.render_device(sort=sort, pass_first=0, pass_count=1)
-            dev_s = live = launches = tr_ms = so_ms = 0
+            dev_s = live = launches = tr_ms = sh_ms = so_ms = 0
         red_s = 0.0
         if dist is not None:
             fb = torch.as_tensor(_DevBuf(ptr, n_floats), device=f"cuda:{local_rank}")
@@ -273,7 +274,7 @@ def main():
             e1.record()
             e1.synchronize()
             red_s = e0.elapsed_time(e1) * 1e-3
-        return dev_s + red_s, live, launches, tr_ms, so_ms, red_s
+        return dev_s + red_s, live, launches, tr_ms, so_ms, red_s, sh_ms
 
     def frame_e2e():
         """The reference-facing call with host buffers: upload (BVH packing + H2D), render, D2H of the sums."""
@@ -297,7 +298,9 @@ def main():
     s1 = r.last_stats
     n_int = s1.internal_visits / max(1, s1.live_ray_bounces)
     n_tri = s1.triangle_tests / max(1, s1.live_ray_bounces)
-    bytes_per_unit = 104.0 + 64.0 * n_int + 48.0 * n_tri
+    bytes_per_unit = 104.0 + 64.0 * n_int + 48.0 * n_tri  # the whole bounce (ray state r/w + key + BVH records)
+    # the dominant kernel (trace_rays_kernel) alone: ray read 32 B + hit record 8 B + BVH records
+    trace_bytes_per_unit = 40.0 + 64.0 * n_int + 48.0 * n_tri
 
     for _ in range(args.warmup):
         frame()
@@ -316,6 +319,7 @@ def main():
     tr_ms = sum(p[3] for p in per_step)
     so_ms = sum(p[4] for p in per_step)
     red_s = sum(p[5] for p in per_step)
+    sh_ms = sum(p[6] for p in per_step)
 
     # e2e: warm once, then time K steps (wall clock around the public call, barrier + sync on both sides)
     frame_e2e()
@@ -347,9 +351,9 @@ def main():
     except OSError:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    # dominant kernel = bounce_kernel: algorithmic bytes of rank 0's launches / their summed CUDA-event durations
+    # dominant kernel = trace_rays_kernel: algorithmic bytes of rank 0's launches / their summed CUDA-event durations
     live_rank0 = sum(p[1] for p in per_step)
-    achieved = live_rank0 * bytes_per_unit / max(1e-9, tr_ms * 1e-3) * 1e-9
+    achieved = live_rank0 * trace_bytes_per_unit / max(1e-9, tr_ms * 1e-3) * 1e-9
     line = {
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -363,10 +367,12 @@ def main():
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
-                     "kernel": "bounce_kernel", "bytes_per_ray_bounce": bytes_per_unit, "n_int": n_int, "n_tri": n_tri,
+                     "kernel": "trace_rays_kernel", "bytes_per_ray_bounce": trace_bytes_per_unit, "n_int": n_int, "n_tri": n_tri,
+                     "whole_bounce_bytes_per_ray_bounce": bytes_per_unit,
+                     "whole_step_achieved": live_rank0 * bytes_per_unit / max(1e-9, sum(p[0] for p in per_step)) * 1e-9,
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
                      "kernel_share_of_step": tr_ms * 1e-3 / max(1e-9, sum(p[0] for p in per_step))},
-        "breakdown_ms_per_step": {"bounce_kernels": tr_ms / args.steps, "reorder": so_ms / args.steps, "nccl_reduce": red_s / args.steps * 1e3,
+        "breakdown_ms_per_step": {"trace_kernels": tr_ms / args.steps, "shade_kernels": sh_ms / args.steps, "reorder": so_ms / args.steps, "nccl_reduce": red_s / args.steps * 1e3,
                                   "wall": wall / args.steps * 1e3},
     }
     if world == 1 and not args.no_cpu_baseline and os.path.exists(REF_BIN):
@@ -376,13 +382,14 @@ def main():
         line["cpu_baseline"] = {"value": ratio * w * h * s_spp / sec * 1e-6, "unit": "Mrays/s", "cores": threads, "kind": "reference",
                                 "sample": f"{w}x{h} x {s_spp} spp of the workload, raytracing_ref cpu no_gpu, {sec:.2f} s"}
     if world == 1 and not args.no_ref_gpu and os.path.exists(REF_BIN):
-        rw, rh = (w, h) if w * h <= 1_000_000 else (1000, 1000)
+        rw, rh = w, h
         tg = ref_gpu_timing(scene_name, rw, rh, bounces)
         lpp = live / args.steps / (w * h * spp)
-        ref = {"config": f"{scene_name}.scene {rw}x{rh}, GPU Took at 100 and 300 spp", "gpu_took_s": tg}
+        lo, hi = sorted(tg)
+        ref = {"config": f"{scene_name}.scene {rw}x{rh}, `GPU Took` at {lo} and {hi} spp (slope = steady state)", "gpu_took_s": tg}
         for mode in ("sort", "no_sort"):
-            if tg[100].get(mode) and tg[300].get(mode):
-                slope = (tg[300][mode] - tg[100][mode]) / 200.0
+            if tg[lo].get(mode) and tg[hi].get(mode):
+                slope = (tg[hi][mode] - tg[lo][mode]) / float(hi - lo)
                 ref[f"{mode}_mrays_per_s_steady"] = lpp * rw * rh / max(slope, 1e-9) * 1e-6
         line["reference_gpu_sm100a"] = ref
     print(json.dumps(line))

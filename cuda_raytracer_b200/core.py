@@ -55,11 +55,15 @@ class Stats(C.Structure):
     _fields_ = [("loop_seconds", C.c_double), ("total_seconds", C.c_double), ("primary_rays", C.c_int64),
                 ("live_ray_bounces", C.c_int64), ("internal_visits", C.c_int64), ("triangle_tests", C.c_int64),
                 ("sorted_pairs", C.c_int64), ("kernel_launches", C.c_int32), ("passes", C.c_int32),
-                ("trace_shade_ms", C.c_double), ("sort_ms", C.c_double), ("live_per_bounce", C.c_int64 * 32)]
+                ("trace_ms", C.c_double), ("shade_ms", C.c_double), ("sort_ms", C.c_double), ("live_per_bounce", C.c_int64 * 32),
+                ("trace_ms_per_bounce", C.c_double * 32), ("shade_ms_per_bounce", C.c_double * 32)]
 
     def as_dict(self):
-        d = {k: getattr(self, k) for k, _ in self._fields_ if k != "live_per_bounce"}
+        arrays = ("live_per_bounce", "trace_ms_per_bounce", "shade_ms_per_bounce")
+        d = {k: getattr(self, k) for k, _ in self._fields_ if k not in arrays}
         d["live_per_bounce"] = [int(v) for v in self.live_per_bounce]
+        d["trace_ms_per_bounce"] = [float(v) for v in self.trace_ms_per_bounce]
+        d["shade_ms_per_bounce"] = [float(v) for v in self.shade_ms_per_bounce]
         return d
 
 

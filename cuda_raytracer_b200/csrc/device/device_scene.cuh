@@ -71,6 +71,7 @@ struct RenderTotals {
 
 struct BounceArgs {
     RayQueue in, out;
+    float2 *hits;           // hit record {t, prim as int bits} per position of the input queue (trace -> shade)
     const uint32_t *order;  // optional permutation of the input queue (reorder pass), else nullptr
     uint32_t *keys_out;     // optional: reorder key of every ray written to `out`
     PassCounters *pc;
@@ -83,6 +84,8 @@ struct BounceArgs {
     uint32_t proc_seed;     // 279220567 * (remaining*20+bounce) (raytracing.cu:89,236)
     unsigned long long pcg_inc;  // 820957824423429 | 1 for stream 0 (random.cuh:28)
     int32_t key_bits;
+    uint32_t trace_batch, trace_refill_below;  // TraceTuning
+    int32_t stack_depth;    // entries per thread of the shared-memory traversal stack (= packed BVH depth, rounded up)
 };
 
 }  // namespace rtd

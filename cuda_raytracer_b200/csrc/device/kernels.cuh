@@ -1,10 +1,12 @@
 // Kernels of the render core. One translation unit (rt_core.cu) includes this file.
 //
-//   bounce_kernel    one bounce of the wavefront: [generate |  fetch] -> closest hit -> shade -> accumulate radiance
-//                    -> compact survivors into the next queue (+ optional reorder key). Persistent CTAs, warp-level
-//                    work fetch from a global cursor.                       (cuda_process_rays raytracing.cu:83-94,
-//                    cuda_generate_initial_rays :76-81, cuda_accumulate_rays :96-107, Scene::process_ray scene.cu:320-487)
-//   trace_kernel     closest hit only (parity hook for Scene::bvh_closest_hit_distance)
+//   trace_rays_kernel  closest hit of every ray of a bounce (bounce 0 generates its rays in place): persistent warps,
+//                      per-lane refill from a global cursor, while-while walk of the packed BVH.
+//                      (cuda_generate_initial_rays raytracing.cu:76-81, Scene::bvh_closest_hit_distance scene.cu:134-241)
+//   shade_kernel       miss / hit shading, radiance accumulation, compaction of survivors into the next queue
+//                      (+ reorder key).  (cuda_process_rays raytracing.cu:83-94, Scene::process_ray scene.cu:320-487,
+//                      cuda_accumulate_rays :96-107)
+//   trace_kernel       closest hit on caller rays (parity hook for Scene::bvh_closest_hit_distance; same tracer)
 //   generate_kernel / process_kernel   reference-layout hooks for Scene::generate_initial_rays / Scene::process_ray
 //   bloom_* / tonemap_kernel           raytracing.cu:21-74 / :286-303
 #pragma once
@@ -17,10 +19,31 @@
 namespace rtd {
 
 constexpr int kBlock = 128;        // threads per CTA of the traversal kernels
-constexpr int kBlocksPerSM = 6;    // 6 x 32 KB of stack = 192 KB shared memory per SM, <= 85 registers per thread
-constexpr int kFetchRounds = 4;    // a warp claims 4 x 32 consecutive queue slots per atomic
+constexpr int kBlocksPerSM = 6;       // shared-memory stack variant: 6 x 32 KB at full depth
+constexpr int kBlocksPerSMLocal = 8;  // local-memory stack variant: 32 warps per SM, <= 64 registers per thread
 
 __device__ __forceinline__ uint32_t lanemask_lt() { return (1u << (threadIdx.x & 31)) - 1u; }
+
+// Warp-aggregated accumulation: consecutive queue positions mostly belong to the same pixel (rays_per_pixel samples
+// in a row, and compaction keeps the order), so each maximal run of equal pixels inside the warp is summed with
+// shuffles and only its first lane issues the atomics. Must be called by all 32 lanes.
+__device__ __forceinline__ void add_radiance(float *framebuffer, uint32_t pixel, float3 c);
+__device__ __forceinline__ void add_radiance_warp(float *framebuffer, uint32_t pixel, float3 c)
+{
+    constexpr uint32_t FULL = 0xffffffffu;
+    const uint32_t lane = threadIdx.x & 31u;
+    if (!__any_sync(FULL, c.x != 0.0f || c.y != 0.0f || c.z != 0.0f)) return;
+    const uint32_t prev = __shfl_up_sync(FULL, pixel, 1);
+    const bool head = lane == 0 || prev != pixel;
+    const uint32_t seg = __popc(__ballot_sync(FULL, head) & (0xffffffffu >> (31u - lane)));
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const float x = __shfl_down_sync(FULL, c.x, off), y = __shfl_down_sync(FULL, c.y, off), z = __shfl_down_sync(FULL, c.z, off);
+        const uint32_t s2 = __shfl_down_sync(FULL, seg, off);
+        if (lane + off < 32u && s2 == seg) { c.x += x; c.y += y; c.z += z; }
+    }
+    if (head) add_radiance(framebuffer, pixel, c);
+}
 
 __device__ __forceinline__ void add_radiance(float *framebuffer, uint32_t pixel, float3 c)
 {
@@ -29,123 +52,174 @@ __device__ __forceinline__ void add_radiance(float *framebuffer, uint32_t pixel,
     if (c.z != 0.0f) atomicAdd(framebuffer + 3 * (size_t)pixel + 2, c.z);
 }
 
-template <bool FIRST, bool STATS>
-__global__ void __launch_bounds__(kBlock, kBlocksPerSM) bounce_kernel(const DeviceScene sc, const BounceArgs a)
+// ---- the wavefront pair of one bounce ------------------------------------------------------------------------------
+// trace_rays_kernel: closest hit of every ray of the bounce's queue -> hit record {t, prim} per queue position.
+// Persistent warps, per-lane refill (traverse.cuh). Bounce 0 generates its rays from the ray id instead of reading
+// them (Scene::generate_initial_rays is ~40 instructions; a 40-byte round trip through HBM costs more).
+template <bool FIRST>
+struct QueueTraceIO {
+    const DeviceScene &sc;
+    const BounceArgs &a;
+    __device__ __forceinline__ bool load(uint32_t i, float3 &o, float3 &d, float &closest, int &prim) const
+    {
+        if (FIRST) {
+            if (!generate_ray(sc, i, a.rays_per_pixel, a.gen_seed, a.pcg_inc, o, d)) return false;
+        } else {
+            const uint32_t slot = a.order ? __ldg(a.order + i) : i;
+            const float4 ra = a.in.qa[slot], rb = a.in.qb[slot];
+            o = f3(ra.x, ra.y, ra.z);
+            d = f3(ra.w, rb.x, rb.y);
+        }
+        intersect_spheres(sc, o, d, closest, prim);
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, float closest, int prim) const
+    {
+        a.hits[i] = make_float2(closest, __int_as_float(prim));
+    }
+};
+
+template <bool STATS>
+__device__ __forceinline__ void flush_trace_counters(const TraceCounters &ctr, RenderTotals *totals)
 {
-    __shared__ SharedStack<kBlock> stack;
+    if (!STATS) return;
+    uint32_t iv = ctr.internal_visits, tt = ctr.triangle_tests;
+    for (int off = 16; off > 0; off >>= 1) {
+        iv += __shfl_xor_sync(0xffffffffu, iv, off);
+        tt += __shfl_xor_sync(0xffffffffu, tt, off);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(&totals->internal_visits, (unsigned long long)iv);
+        atomicAdd(&totals->triangle_tests, (unsigned long long)tt);
+    }
+}
+
+template <bool FIRST, bool STATS, bool SMEM>
+__global__ void __launch_bounds__(kBlock, SMEM ? kBlocksPerSM : kBlocksPerSMLocal) trace_rays_kernel(const DeviceScene sc, const BounceArgs a)
+{
+    extern __shared__ uint32_t stack_smem[];
+    const uint32_t n_in = FIRST ? a.n_first : a.pc->count[a.bounce];
+    TraceCounters ctr;
+    QueueTraceIO<FIRST> io{sc, a};
+    if (SMEM) {
+        SmemStack<kBlock> stack(stack_smem, a.stack_depth);
+        trace_persistent<STATS>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below});
+    } else {
+        LocalStack stack;
+        trace_persistent<STATS>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below});
+    }
+    flush_trace_counters<STATS>(ctr, a.totals);
+}
+
+// shade_kernel: one thread per ray of the bounce: miss -> sky radiance, hit -> emission + material scatter; radiance
+// goes to the framebuffer at once, survivors are compacted into the next queue (+ optional reorder key).
+// (cuda_process_rays raytracing.cu:83-94, Scene::process_ray scene.cu:376-487, cuda_accumulate_rays :96-107)
+constexpr int kShadeBlock = 256;
+
+template <bool FIRST>
+__global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc, const BounceArgs a)
+{
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n_in = FIRST ? a.n_first : a.pc->count[a.bounce];
-    uint32_t *cursor = &a.pc->cursor[a.bounce];
     uint32_t *out_count = &a.pc->count[a.bounce + 1];
     const bool write_out = a.out.qa != nullptr;
-    TraceCounters ctr;
 
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         atomicAdd(&a.totals->live_ray_bounces, (unsigned long long)n_in);
         atomicAdd(&a.totals->live_per_bounce[a.bounce], (unsigned long long)n_in);
     }
-
-    for (;;) {
-        uint32_t base = 0;
-        if (lane == 0) base = atomicAdd(cursor, 32u * kFetchRounds);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n_in) break;
-
-#pragma unroll 1
-        for (int round = 0; round < kFetchRounds; round++) {
-            const uint32_t first = base + 32u * round;
-            if (first >= n_in) break;
-            const uint32_t i = first + lane;
-            bool active = i < n_in;
-
-            float3 o = f3(0, 0, 0), d = f3(0, 0, 1), T = f3(1, 1, 1);
-            uint32_t id = i;
-            if (active) {
-                if (FIRST) {
-                    active = generate_ray(sc, id, a.rays_per_pixel, a.gen_seed, a.pcg_inc, o, d);
-                } else {
-                    const uint32_t slot = a.order ? __ldg(a.order + i) : i;
-                    const float4 ra = a.in.qa[slot], rb = a.in.qb[slot];
-                    const float2 rc = a.in.qc[slot];
-                    o = f3(ra.x, ra.y, ra.z);
-                    d = f3(ra.w, rb.x, rb.y);
-                    T = f3(rb.z, rb.w, rc.x);
-                    id = __float_as_uint(rc.y);
-                }
-            }
-
-            bool alive = false;
-            if (active) {
-                float closest = kMissT;
-                int prim = -1;
-                intersect_spheres(sc, o, d, closest, prim);
-                traverse_bvh<kBlock, STATS>(sc, o, d, closest, prim, stack, ctr);
-
-                const uint32_t pixel = id / (uint32_t)a.rays_per_pixel;
-                if (prim < 0) {
-                    add_radiance(a.framebuffer, pixel, shade_miss(sc, d) * T);
-                } else {
-                    Pcg rng = pcg_seed(id * 4137874753u + a.proc_seed, a.pcg_inc);  // raytracing.cu:89 with slot == ray id
-                    float3 emitted;
-                    shade_hit(sc, o, d, closest, prim, T, rng, emitted);
-                    add_radiance(a.framebuffer, pixel, emitted);
-                    alive = !is_zero(T);  // a path dies only when its throughput is exactly zero (Q10)
-                }
-            }
-
-            if (write_out) {  // next-bounce compaction: one atomic per warp, survivors stay contiguous
-                const uint32_t mask = __ballot_sync(0xffffffffu, alive);
-                if (mask) {
-                    uint32_t pos = 0;
-                    if (lane == 0) pos = atomicAdd(out_count, (uint32_t)__popc(mask));
-                    pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(mask & lanemask_lt());
-                    if (alive) {
-                        a.out.qa[pos] = make_float4(o.x, o.y, o.z, d.x);
-                        a.out.qb[pos] = make_float4(d.y, d.z, T.x, T.y);
-                        a.out.qc[pos] = make_float2(T.z, __uint_as_float(id));
-                        if (a.keys_out) a.keys_out[pos] = reorder_key(sc.key_min, sc.key_inv_extent, o, d, a.key_bits);
-                    }
-                }
+    const uint32_t n_round = (n_in + 31u) & ~31u;  // whole warps iterate together (ballots below)
+    for (uint32_t i = blockIdx.x * kShadeBlock + threadIdx.x; i < n_round; i += gridDim.x * kShadeBlock) {
+        bool active = i < n_in;
+        float3 o = f3(0, 0, 0), d = f3(0, 0, 1), T = f3(1, 1, 1);
+        uint32_t id = i;
+        if (active) {
+            if (FIRST) {
+                active = generate_ray(sc, id, a.rays_per_pixel, a.gen_seed, a.pcg_inc, o, d);
+            } else {
+                const uint32_t slot = a.order ? __ldg(a.order + i) : i;
+                const float4 ra = a.in.qa[slot], rb = a.in.qb[slot];
+                const float2 rc = a.in.qc[slot];
+                o = f3(ra.x, ra.y, ra.z);
+                d = f3(ra.w, rb.x, rb.y);
+                T = f3(rb.z, rb.w, rc.x);
+                id = __float_as_uint(rc.y);
             }
         }
-    }
-
-    if (STATS) {
-        uint32_t iv = ctr.internal_visits, tt = ctr.triangle_tests;
-        for (int off = 16; off > 0; off >>= 1) {
-            iv += __shfl_xor_sync(0xffffffffu, iv, off);
-            tt += __shfl_xor_sync(0xffffffffu, tt, off);
+        bool alive = false;
+        float3 radiance = f3(0, 0, 0);
+        uint32_t pixel = 0xFFFFFFFFu;
+        if (active) {
+            const float2 h = a.hits[i];
+            const float closest = h.x;
+            const int prim = __float_as_int(h.y);
+            pixel = id / (uint32_t)a.rays_per_pixel;
+            if (prim < 0) {
+                radiance = shade_miss(sc, d) * T;
+            } else {
+                Pcg rng = pcg_seed(id * 4137874753u + a.proc_seed, a.pcg_inc);  // raytracing.cu:89 with slot == ray id
+                shade_hit(sc, o, d, closest, prim, T, rng, radiance);
+                alive = !is_zero(T);  // a path dies only when its throughput is exactly zero (Q10)
+            }
         }
-        if (lane == 0) {
-            atomicAdd(&a.totals->internal_visits, (unsigned long long)iv);
-            atomicAdd(&a.totals->triangle_tests, (unsigned long long)tt);
+        add_radiance_warp(a.framebuffer, pixel, radiance);
+        if (write_out) {  // next-bounce compaction: one atomic per warp, survivors stay contiguous
+            const uint32_t mask = __ballot_sync(0xffffffffu, alive);
+            if (mask) {
+                uint32_t pos = 0;
+                if (lane == 0) pos = atomicAdd(out_count, (uint32_t)__popc(mask));
+                pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(mask & lanemask_lt());
+                if (alive) {
+                    a.out.qa[pos] = make_float4(o.x, o.y, o.z, d.x);
+                    a.out.qb[pos] = make_float4(d.y, d.z, T.x, T.y);
+                    a.out.qc[pos] = make_float2(T.z, __uint_as_float(id));
+                    if (a.keys_out) a.keys_out[pos] = reorder_key(sc.key_min, sc.key_inv_extent, o, d, a.key_bits);
+                }
+            }
         }
     }
 }
 
 // ---- parity hooks: same device functions, reference-layout I/O ---------------------------------------------------
 
-template <bool STATS>
-__global__ void __launch_bounds__(kBlock, kBlocksPerSM) trace_kernel(const DeviceScene sc, const float *__restrict__ rays6, uint32_t n,
-                                                                      int with_spheres, int *__restrict__ out_prim,
-                                                                      float *__restrict__ out_t, RenderTotals *totals)
-{
-    __shared__ SharedStack<kBlock> stack;
-    TraceCounters ctr;
-    for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n; i += gridDim.x * kBlock) {
+struct Rays6IO {  // rt_trace_closest: rays {o, d} in, {prim, t} out
+    const DeviceScene &sc;
+    const float *__restrict__ rays6;
+    int with_spheres;
+    int *__restrict__ out_prim;
+    float *__restrict__ out_t;
+    __device__ __forceinline__ bool load(uint32_t i, float3 &o, float3 &d, float &closest, int &prim) const
+    {
         const float *r = rays6 + 6 * (size_t)i;
-        float3 o = f3(r[0], r[1], r[2]), d = f3(r[3], r[4], r[5]);
-        float closest = kMissT;
-        int prim = -1;
+        o = f3(r[0], r[1], r[2]);
+        d = f3(r[3], r[4], r[5]);
         if (with_spheres) intersect_spheres(sc, o, d, closest, prim);
-        traverse_bvh<kBlock, STATS>(sc, o, d, closest, prim, stack, ctr);
+        return true;
+    }
+    __device__ __forceinline__ void store(uint32_t i, float closest, int prim) const
+    {
         out_prim[i] = prim;
         out_t[i] = closest;
     }
-    if (STATS) {
-        atomicAdd(&totals->internal_visits, (unsigned long long)ctr.internal_visits);
-        atomicAdd(&totals->triangle_tests, (unsigned long long)ctr.triangle_tests);
+};
+
+template <bool STATS, bool SMEM>
+__global__ void __launch_bounds__(kBlock, SMEM ? kBlocksPerSM : kBlocksPerSMLocal) trace_kernel(const DeviceScene sc, const float *__restrict__ rays6, uint32_t n,
+                                                                      int with_spheres, int *__restrict__ out_prim,
+                                                                      float *__restrict__ out_t, uint32_t *cursor, int stack_depth,
+                                                                      TraceTuning tune, RenderTotals *totals)
+{
+    extern __shared__ uint32_t stack_smem[];
+    TraceCounters ctr;
+    Rays6IO io{sc, rays6, with_spheres, out_prim, out_t};
+    if (SMEM) {
+        SmemStack<kBlock> stack(stack_smem, stack_depth);
+        trace_persistent<STATS>(sc, n, cursor, stack, io, ctr, tune);
+    } else {
+        LocalStack stack;
+        trace_persistent<STATS>(sc, n, cursor, stack, io, ctr, tune);
     }
+    flush_trace_counters<STATS>(ctr, totals);
 }
 
 // 12 floats per ray: origin, direction, transmitted = 1, collected = 0 (RayData, scene.cuh:61-68)

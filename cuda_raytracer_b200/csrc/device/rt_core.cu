@@ -40,7 +40,10 @@ struct rt_ctx {
     uint8_t *d_rgb8 = nullptr;
     size_t fb_pixels = 0;
     RayQueue queue[2] = {};
+    float2 *d_hits = nullptr;  // {t, prim} per queue position of the bounce in flight
     size_t queue_capacity = 0;
+    int stack_mode = 0;        // 0 = shared-memory traversal stack, 1 = local-memory stack (RT_STACK=local)
+    uint32_t trace_batch = kBatch, trace_refill_below = kRefillBelow;  // RT_BATCH / RT_REFILL override
     uint32_t *d_keys[2] = {nullptr, nullptr}, *d_vals[2] = {nullptr, nullptr};
     size_t sort_capacity = 0;
     uint32_t *d_sort_scratch = nullptr;  // hist + tile counters + tile status
@@ -216,6 +219,9 @@ extern "C" int rt_create(rt_ctx **out, int device)
     RT_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
     RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    if (const char *e = std::getenv("RT_STACK")) ctx->stack_mode = std::strcmp(e, "local") == 0 ? 1 : 0;
+    if (const char *e = std::getenv("RT_BATCH")) ctx->trace_batch = (uint32_t)std::min(4096, std::max(4, std::atoi(e)));
+    if (const char *e = std::getenv("RT_REFILL")) ctx->trace_refill_below = (uint32_t)std::min(33, std::max(1, std::atoi(e)));
     RT_CUDA(ctx, cudaEventCreate(&ctx->ev_start));
     RT_CUDA(ctx, cudaEventCreate(&ctx->ev_stop));
     RT_CUDA(ctx, cudaMalloc(&ctx->d_pc, sizeof(PassCounters)));
@@ -235,6 +241,7 @@ extern "C" void rt_destroy(rt_ctx *ctx)
         release(ctx->queue[i].qa); release(ctx->queue[i].qb); release(ctx->queue[i].qc);
         release(ctx->d_keys[i]); release(ctx->d_vals[i]);
     }
+    release(ctx->d_hits);
     release(ctx->d_sort_scratch); release(ctx->d_pc); release(ctx->d_totals);
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
@@ -352,7 +359,9 @@ int ensure_queues(rt_ctx *ctx, size_t rays, bool sort)
 {
     if (rays > ctx->queue_capacity) {
         for (int i = 0; i < 2; i++) { release(ctx->queue[i].qa); release(ctx->queue[i].qb); release(ctx->queue[i].qc); }
+        release(ctx->d_hits);
         ctx->queue_capacity = 0;
+        RT_CUDA(ctx, cudaMalloc(&ctx->d_hits, rays * sizeof(float2)));
         for (int i = 0; i < 2; i++) {
             RT_CUDA(ctx, cudaMalloc(&ctx->queue[i].qa, rays * sizeof(float4)));
             RT_CUDA(ctx, cudaMalloc(&ctx->queue[i].qb, rays * sizeof(float4)));
@@ -416,11 +425,32 @@ int enqueue_sort(rt_ctx *ctx, const uint32_t *count_ptr, size_t bound, int bits,
 // ---- the pass loop (gpu_raytrace, raytracing.cu:170-284) ------------------------------------------------------
 namespace {
 
+// Shared-memory bytes of the traversal stack for one CTA (0 for the local-memory variant).
+size_t stack_bytes(const rt_ctx *ctx) { return ctx->stack_mode ? 0 : (size_t)std::max(4, ctx->packed_depth) * kBlock * 8; }
+
 template <bool FIRST>
-void launch_bounce(bool stats, int grid, cudaStream_t stream, const DeviceScene &ds, const BounceArgs &a)
+void launch_trace(const rt_ctx *ctx, bool stats, int grid, const BounceArgs &a)
 {
-    if (stats) bounce_kernel<FIRST, true><<<grid, kBlock, 0, stream>>>(ds, a);
-    else bounce_kernel<FIRST, false><<<grid, kBlock, 0, stream>>>(ds, a);
+    const size_t smem = stack_bytes(ctx);
+    if (ctx->stack_mode) {
+        if (stats) trace_rays_kernel<FIRST, true, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->ds, a);
+        else trace_rays_kernel<FIRST, false, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->ds, a);
+    } else {
+        if (stats) trace_rays_kernel<FIRST, true, true><<<grid, kBlock, smem, ctx->stream>>>(ctx->ds, a);
+        else trace_rays_kernel<FIRST, false, true><<<grid, kBlock, smem, ctx->stream>>>(ctx->ds, a);
+    }
+}
+
+// Persistent grid of the tracer: every SM filled to the occupancy the stack variant allows.
+int trace_grid_size(rt_ctx *ctx, int *out)
+{
+    int per_sm = 0;
+    if (ctx->stack_mode)
+        RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_rays_kernel<false, false, false>, kBlock, 0));
+    else
+        RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_rays_kernel<false, false, true>, kBlock, stack_bytes(ctx)));
+    *out = ctx->sm_count * std::max(1, per_sm);
+    return RT_OK;
 }
 
 int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
@@ -439,7 +469,9 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     const int pass_end = opts.pass_count > 0 ? std::min(total_passes, pass_first + opts.pass_count) : total_passes;
     const bool collect = opts.collect_stats != 0;
     const bool timing = (opts.reserved & 1) != 0;  // CUDA-event pair around every bounce kernel and every reorder pass
-    std::vector<int> ev_kind;                       // 0 = bounce kernel, 1 = reorder
+    std::vector<int> ev_kind;                       // 0 = trace kernel, 1 = reorder, 2 = shade kernel
+    std::vector<int> ev_bounce;
+    int cur_bounce = 0;
     auto mark = [&](int kind) -> int {
         if (!timing) return RT_OK;
         size_t k = ev_kind.size();
@@ -449,6 +481,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             ctx->ev_pool.push_back(e);
         }
         ev_kind.push_back(kind);
+        ev_bounce.push_back(cur_bounce);
         return cudaEventRecord(ctx->ev_pool[k], ctx->stream) == cudaSuccess ? RT_OK : RT_ERR_CUDA;
     };
     const bool sort = opts.sort != 0 && ctx->bounces > 1;
@@ -463,9 +496,9 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     if (rc != RT_OK) return rc;
     if ((rc = ensure_queues(ctx, pixels * (size_t)std::min(pass_spp, std::max(1, ctx->ray_count)), sort)) != RT_OK) return rc;
 
-    int blocks_per_sm = 0;
-    RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, bounce_kernel<false, false>, kBlock, 0));
-    const int grid = ctx->sm_count * std::max(1, blocks_per_sm);
+    int grid = 0;
+    if ((rc = trace_grid_size(ctx, &grid)) != RT_OK) return rc;
+    const int shade_grid_max = ctx->sm_count * 8;
 
     RT_CUDA(ctx, cudaMemsetAsync(ctx->d_fb, 0, pixels * 3 * sizeof(float), ctx->stream));
     RT_CUDA(ctx, cudaMemsetAsync(ctx->d_totals, 0, sizeof(RenderTotals), ctx->stream));
@@ -483,6 +516,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         const uint32_t *order = nullptr;
         for (int b = 0; b < ctx->bounces; b++) {
             BounceArgs a{};
+            cur_bounce = b;
             a.in = ctx->queue[(b + 1) & 1];
             a.out = (b + 1 < ctx->bounces) ? ctx->queue[b & 1] : RayQueue{nullptr, nullptr, nullptr};
             a.order = order;
@@ -497,11 +531,22 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             a.proc_seed = 279220567u * (uint32_t)(remaining * 20 + b);                 // raytracing.cu:89,236
             a.pcg_inc = pcg_inc;
             a.key_bits = key_bits;
+            a.hits = ctx->d_hits;
+            a.stack_depth = std::max(4, ctx->packed_depth);
+            a.trace_batch = ctx->trace_batch;
+            a.trace_refill_below = ctx->trace_refill_below;
+            // the live count of bounce b > 0 exists only on the device: size the grids for the pass's upper bound
+            const int shade_grid = (int)std::min<size_t>((size_t)shade_grid_max, ((size_t)total + kShadeBlock - 1) / kShadeBlock);
+            const int t_grid = (int)std::min<size_t>((size_t)grid, ((size_t)total + kBlock - 1) / kBlock);
             if ((rc = mark(0)) != RT_OK) return fail(ctx, rc, "event record failed");
-            if (b == 0) launch_bounce<true>(collect, grid, ctx->stream, ctx->ds, a);
-            else launch_bounce<false>(collect, grid, ctx->stream, ctx->ds, a);
+            if (b == 0) launch_trace<true>(ctx, collect, t_grid, a);
+            else launch_trace<false>(ctx, collect, t_grid, a);
             if ((rc = mark(0)) != RT_OK) return fail(ctx, rc, "event record failed");
-            launches++;
+            if ((rc = mark(2)) != RT_OK) return fail(ctx, rc, "event record failed");
+            if (b == 0) shade_kernel<true><<<shade_grid, kShadeBlock, 0, ctx->stream>>>(ctx->ds, a);
+            else shade_kernel<false><<<shade_grid, kShadeBlock, 0, ctx->stream>>>(ctx->ds, a);
+            if ((rc = mark(2)) != RT_OK) return fail(ctx, rc, "event record failed");
+            launches += 2;
             order = nullptr;
             if (a.keys_out) {
                 uint32_t *sk, *sv;
@@ -537,7 +582,9 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         for (size_t k = 0; k + 1 < ev_kind.size(); k += 2) {
             float e_ms = 0;
             RT_CUDA(ctx, cudaEventElapsedTime(&e_ms, ctx->ev_pool[k], ctx->ev_pool[k + 1]));
-            (ev_kind[k] == 0 ? stats->trace_shade_ms : stats->sort_ms) += e_ms;
+            (ev_kind[k] == 0 ? stats->trace_ms : ev_kind[k] == 2 ? stats->shade_ms : stats->sort_ms) += e_ms;
+            if (ev_kind[k] == 0) stats->trace_ms_per_bounce[ev_bounce[k]] += e_ms;
+            if (ev_kind[k] == 2) stats->shade_ms_per_bounce[ev_bounce[k]] += e_ms;
         }
         stats->total_seconds = std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - wall0).count();
     }
@@ -627,13 +674,25 @@ extern "C" int rt_trace_closest(rt_ctx *ctx, const float *rays6, int32_t n, int3
     RT_CUDA(ctx, cudaMalloc(&t.p, (size_t)n * sizeof(float)));
     RT_CUDA(ctx, cudaMemcpyAsync(rays.p, rays6, (size_t)n * 6 * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
     RT_CUDA(ctx, cudaMemsetAsync(ctx->d_totals, 0, sizeof(RenderTotals), ctx->stream));
+    RT_CUDA(ctx, cudaMemsetAsync(ctx->d_pc, 0, sizeof(PassCounters), ctx->stream));
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
-    if (stats)
-        trace_kernel<true><<<hook_grid(ctx, n), kBlock, 0, ctx->stream>>>(ctx->ds, (const float *)rays.p, (uint32_t)n, with_spheres,
-                                                                         (int *)prim.p, (float *)t.p, ctx->d_totals);
-    else
-        trace_kernel<false><<<hook_grid(ctx, n), kBlock, 0, ctx->stream>>>(ctx->ds, (const float *)rays.p, (uint32_t)n, with_spheres,
-                                                                          (int *)prim.p, (float *)t.p, ctx->d_totals);
+    {
+        int grid = 0, rc = trace_grid_size(ctx, &grid);
+        if (rc != RT_OK) return rc;
+        grid = (int)std::min<size_t>((size_t)grid, ((size_t)n + kBlock - 1) / kBlock);
+        const size_t smem = stack_bytes(ctx);
+        const int depth = std::max(4, ctx->packed_depth);
+        uint32_t *cursor = &ctx->d_pc->cursor[0];
+        const TraceTuning tune{ctx->trace_batch, ctx->trace_refill_below};
+        const float *r6 = (const float *)rays.p;
+        if (ctx->stack_mode) {
+            if (stats) trace_kernel<true, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->ds, r6, (uint32_t)n, with_spheres, (int *)prim.p, (float *)t.p, cursor, depth, tune, ctx->d_totals);
+            else trace_kernel<false, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->ds, r6, (uint32_t)n, with_spheres, (int *)prim.p, (float *)t.p, cursor, depth, tune, ctx->d_totals);
+        } else {
+            if (stats) trace_kernel<true, true><<<grid, kBlock, smem, ctx->stream>>>(ctx->ds, r6, (uint32_t)n, with_spheres, (int *)prim.p, (float *)t.p, cursor, depth, tune, ctx->d_totals);
+            else trace_kernel<false, true><<<grid, kBlock, smem, ctx->stream>>>(ctx->ds, r6, (uint32_t)n, with_spheres, (int *)prim.p, (float *)t.p, cursor, depth, tune, ctx->d_totals);
+        }
+    }
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
     RT_CUDA(ctx, cudaGetLastError());
     RT_CUDA(ctx, cudaMemcpyAsync(out_prim, prim.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));

@@ -127,4 +127,150 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
     }
 }
 
+// ---- production tracer: persistent warps with per-lane refill ------------------------------------------------------
+//
+// The per-thread loop above keeps a whole warp busy until its LONGEST ray ends; on incoherent bounces ncu showed
+// 5-9 of 32 lanes active per issued instruction (profiles/r1_bounce_fused_lamp1k.md). Here every lane owns one ray
+// at a time and the warp keeps walking while enough lanes are busy; when fewer than kRefillBelow lanes still have
+// a ray, the warp converges, finished lanes take the next rays from the warp's batch (one global atomic per
+// kBatch rays) and the walk resumes ("persistent while-while with dynamic fetch", Aila & Laine 2009, restated for
+// independent thread scheduling: every vote is an explicit *_sync at a point where all 32 lanes arrive).
+//
+// IO policy:  bool load(uint32_t i, float3 &o, float3 &d, float &closest, int &prim)   false = nothing to trace
+//             void store(uint32_t i, float closest, int prim)
+constexpr uint32_t kDoneRef = 0xFFFFFFFFu;  // never a valid leaf ref: start would exceed the 2^27 triangle limit
+constexpr int kBatch = 96;                  // default: rays a warp claims per global atomic
+constexpr int kRefillBelow = 22;            // default: refill when fewer lanes than this still hold a ray
+struct TraceTuning {
+    uint32_t batch;         // rays per claim; the kernel shrinks it when the bounce has fewer rays than batch x warps
+    uint32_t refill_below;
+};
+
+// Stack storage policies. Both are entry-major per warp so the 32 lanes of an access hit 32 banks / one 128-byte line.
+template <int BLOCK>
+struct SmemStack {
+    uint32_t *ref;
+    float *dist;
+    __device__ __forceinline__ SmemStack(uint32_t *base, int depth) : ref(base + threadIdx.x), dist(reinterpret_cast<float *>(base) + (size_t)depth * BLOCK + threadIdx.x) {}
+    __device__ __forceinline__ void push(int sp, uint32_t r, float d) { ref[sp * BLOCK] = r; dist[sp * BLOCK] = d; }
+    __device__ __forceinline__ void get(int sp, uint32_t &r, float &d) const { r = ref[sp * BLOCK]; d = dist[sp * BLOCK]; }
+};
+struct LocalStack {  // thread-local arrays: the hardware interleaves local memory per lane, lines live in L1
+    uint32_t ref[kStackDepth];
+    float dist[kStackDepth];
+    __device__ __forceinline__ void push(int sp, uint32_t r, float d) { ref[sp] = r; dist[sp] = d; }
+    __device__ __forceinline__ void get(int sp, uint32_t &r, float &d) const { r = ref[sp]; d = dist[sp]; }
+};
+
+template <bool STATS, class Stack, class IO>
+__device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t n, uint32_t *cursor, Stack &stack, IO &io,
+                                                 TraceCounters &ctr, TraceTuning tune)
+{
+    constexpr uint32_t FULL = 0xffffffffu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t lt = (1u << lane) - 1u;
+    const float4 *__restrict__ nodes = sc.nodes;
+
+    // Small bounces (late bounces hold ~0.2 % of the pass) are latency-bound: spread them over every resident warp
+    // instead of queueing `batch` rays behind a few warps.
+    const uint32_t warps = gridDim.x * (blockDim.x >> 5);
+    const uint32_t batch = max(4u, min(tune.batch, (n + warps - 1) / warps));
+    const uint32_t refill_below = tune.refill_below;
+    uint32_t pool_next = 0, pool_end = 0;  // warp-uniform: unclaimed part of the current batch
+    bool exhausted = false;                // warp-uniform: the global cursor ran past n
+    bool busy = false;
+    uint32_t slot = 0, cur = kDoneRef;
+    int sp = 0, prim = -1;
+    float closest = kMissT;
+    float3 o = f3(0, 0, 0), d = f3(0, 0, 1), inv = f3(0, 0, 1);
+
+    for (;;) {
+        // ---- refill: all 32 lanes are here ----
+        uint32_t need = __ballot_sync(FULL, !busy);
+        while (need) {
+            if (pool_next == pool_end) {
+                if (exhausted) break;
+                uint32_t b = 0;
+                if (lane == 0) b = atomicAdd(cursor, batch);
+                b = __shfl_sync(FULL, b, 0);
+                if (b >= n) { exhausted = true; break; }
+                pool_next = b;
+                pool_end = min(b + batch, n);
+            }
+            const uint32_t avail = pool_end - pool_next;
+            const uint32_t rank = __popc(need & lt);
+            if (!busy && rank < avail) {
+                slot = pool_next + rank;
+                closest = kMissT;
+                prim = -1;
+                if (io.load(slot, o, d, closest, prim)) {
+                    inv = f3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+                    cur = 0;  // record 0 is the root
+                    sp = 0;
+                    busy = true;
+                }
+            }
+            pool_next += min((uint32_t)__popc(need), avail);
+            need = __ballot_sync(FULL, !busy);
+            if (!need) break;
+            // lanes whose load() declined stay idle this round; lanes beyond `avail` retry on the next batch
+            if (pool_next != pool_end) break;
+        }
+        if (!__any_sync(FULL, busy)) {
+            if (exhausted && pool_next == pool_end) break;
+            continue;
+        }
+
+        // ---- walk: lanes leave individually, the warp reconverges at the __syncwarp below ----
+        while (busy) {
+            // descend through internal records until this lane holds a leaf (or runs dry)
+            while (!(cur & kLeafBit)) {
+                const float4 *nd = nodes + 4 * (size_t)cur;
+                const float4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2);
+                const uint4 q3 = __ldg(reinterpret_cast<const uint4 *>(nd + 3));
+                if (STATS) ctr.internal_visits++;
+                float d0, d1;
+                const bool h0 = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv, closest, d0);
+                const bool h1 = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv, closest, d1);
+                if (h0 && h1) {
+                    const bool zero_near = d0 < d1;
+                    stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
+                    sp++;
+                    cur = zero_near ? q3.x : q3.y;
+                } else if (h0) {
+                    cur = q3.x;
+                } else if (h1) {
+                    cur = q3.y;
+                } else {
+                    float entry;
+                    do {
+                        if (sp == 0) { cur = kDoneRef; break; }
+                        sp--;
+                        stack.get(sp, cur, entry);
+                    } while (entry >= closest);
+                }
+            }
+            if (cur != kDoneRef) {
+                const uint32_t first = cur & kLeafStartMask;
+                const uint32_t count = (cur >> kLeafCountShift) & 15u;
+                if (STATS) ctr.triangle_tests += count;
+                for (uint32_t k = 0; k < count; k++) intersect_triangle(sc.tris, first + k, sc.sphere_count, o, d, closest, prim);
+                float entry;  // pop, culling entries that can no longer beat the current hit (scene.cu:150-153)
+                do {
+                    if (sp == 0) { cur = kDoneRef; break; }
+                    sp--;
+                    stack.get(sp, cur, entry);
+                } while (entry >= closest);
+            }
+            if (cur == kDoneRef) {
+                io.store(slot, closest, prim);
+                busy = false;
+                break;
+            }
+            if (__popc(__activemask()) < refill_below) break;  // heuristic only: correctness never depends on this mask
+        }
+        __syncwarp();
+    }
+}
+
 }  // namespace rtd

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RT_API_VERSION 1
+#define RT_API_VERSION 2
 
 typedef enum rt_status {
     RT_OK = 0,
@@ -75,7 +75,7 @@ typedef struct rt_render_opts {
                               k > 0 = disjoint PCG streams: stream k's `inc` differs (random.cuh:28), for multi-GPU runs
                               that do NOT want pass-identical images */
     int32_t sort_bits;     /* key width for the reorder pass, 0 = default */
-    int32_t reserved;      /* bit 0: time every bounce kernel / reorder pass with CUDA events (rt_stats.trace_shade_ms, sort_ms) */
+    int32_t reserved;      /* bit 0: time every bounce kernel / reorder pass with CUDA events (rt_stats.trace_ms, shade_ms, sort_ms) */
 } rt_render_opts;
 
 typedef struct rt_stats {
@@ -88,9 +88,12 @@ typedef struct rt_stats {
     int64_t sorted_pairs;       /* (key,index) pairs pushed through the reorder pass */
     int32_t kernel_launches;    /* kernels of THIS library launched inside the loop */
     int32_t passes;
-    double trace_shade_ms;      /* CUDA-event sum over the bounce kernels (0 unless rt_render_opts.reserved bit 0) */
-    double sort_ms;
+    double trace_ms;            /* CUDA-event sums per kernel class (0 unless rt_render_opts.reserved bit 0): closest-hit kernels, */
+    double shade_ms;            /* shading + compaction kernels, */
+    double sort_ms;             /* reorder passes */
     int64_t live_per_bounce[32];
+    double trace_ms_per_bounce[32];  /* with reserved bit 0: per-bounce sums over the passes */
+    double shade_ms_per_bounce[32];
 } rt_stats;
 
 typedef struct rt_ctx rt_ctx;

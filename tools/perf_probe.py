@@ -27,8 +27,10 @@ for v in variants:
         if best is None or s.loop_seconds < best.loop_seconds: best = s
     s = best
     mr = s.live_ray_bounces / s.loop_seconds * 1e-6
-    print(f" {v:8s}: loop {s.loop_seconds*1e3:8.2f} ms  {mr:9.1f} Mrays/s  bounce-kernels {s.trace_shade_ms:8.2f} ms  reorder {s.sort_ms:7.2f} ms  launches {s.kernel_launches}  "
-          f"roofline {mr*1e6*(104+64*n_int+48*n_tri)/6557.1e9:.3f}")
+    print(f" {v:8s}: loop {s.loop_seconds*1e3:8.2f} ms  {mr:9.1f} Mrays/s  trace {s.trace_ms:8.2f} ms  shade {s.shade_ms:8.2f} ms  reorder {s.sort_ms:7.2f} ms  launches {s.kernel_launches}  "
+          f"roofline {mr*1e6*(104+64*n_int+48*n_tri)/6543.7e9:.3f}")
+    print("   trace ms/bounce:", " ".join(f"{v:.2f}" for v in s.trace_ms_per_bounce[:bounces]))
+    print("   shade ms/bounce:", " ".join(f"{v:.2f}" for v in s.shade_ms_per_bounce[:bounces]))
 r.close()
 ref = os.path.join(ROOT, "oracle", "_ref", "raytracing_ref")
 if os.path.exists(ref) and "noref" not in sys.argv:
