@@ -84,7 +84,7 @@ struct BounceArgs {
     uint32_t proc_seed;     // 279220567 * (remaining*20+bounce) (raytracing.cu:89,236)
     unsigned long long pcg_inc;  // 820957824423429 | 1 for stream 0 (random.cuh:28)
     int32_t key_bits;
-    uint32_t trace_batch, trace_refill_below;  // TraceTuning
+    uint32_t trace_batch, trace_refill_below, trace_node_min;  // TraceTuning
     int32_t stack_depth;    // entries per thread of the shared-memory traversal stack (= packed BVH depth, rounded up)
 };
 

@@ -66,7 +66,7 @@ struct QueueTraceIO {
             if (!generate_ray(sc, i, a.rays_per_pixel, a.gen_seed, a.pcg_inc, o, d)) return false;
         } else {
             const uint32_t slot = a.order ? __ldg(a.order + i) : i;
-            const float4 ra = a.in.qa[slot], rb = a.in.qb[slot];
+            const float4 ra = __ldcs(a.in.qa + slot), rb = __ldcs(a.in.qb + slot);
             o = f3(ra.x, ra.y, ra.z);
             d = f3(ra.w, rb.x, rb.y);
         }
@@ -75,7 +75,7 @@ struct QueueTraceIO {
     }
     __device__ __forceinline__ void store(uint32_t i, float closest, int prim) const
     {
-        a.hits[i] = make_float2(closest, __int_as_float(prim));
+        __stcs(a.hits + i, make_float2(closest, __int_as_float(prim)));
     }
 };
 
@@ -103,10 +103,10 @@ __global__ void __launch_bounds__(kBlock, SMEM ? kBlocksPerSM : kBlocksPerSMLoca
     QueueTraceIO<FIRST> io{sc, a};
     if (SMEM) {
         SmemStack<kBlock> stack(stack_smem, a.stack_depth);
-        trace_persistent<STATS>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below});
+        trace_persistent<STATS>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below, a.trace_node_min});
     } else {
         LocalStack stack;
-        trace_persistent<STATS>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below});
+        trace_persistent<STATS>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below, a.trace_node_min});
     }
     flush_trace_counters<STATS>(ctr, a.totals);
 }
@@ -128,7 +128,12 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
         atomicAdd(&a.totals->live_ray_bounces, (unsigned long long)n_in);
         atomicAdd(&a.totals->live_per_bounce[a.bounce], (unsigned long long)n_in);
     }
-    const uint32_t n_round = (n_in + 31u) & ~31u;  // whole warps iterate together (ballots below)
+    // whole CTAs iterate together: the compaction below reserves output slots once per CTA and iteration (a single
+    // per-warp atomic on one counter was 50 % of this kernel's stall samples, profiles/r1b_split_lamp1k.md)
+    __shared__ uint32_t warp_count[kShadeBlock / 32];
+    __shared__ uint32_t block_base;
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t n_round = (n_in + kShadeBlock - 1u) / kShadeBlock * kShadeBlock;
     for (uint32_t i = blockIdx.x * kShadeBlock + threadIdx.x; i < n_round; i += gridDim.x * kShadeBlock) {
         bool active = i < n_in;
         float3 o = f3(0, 0, 0), d = f3(0, 0, 1), T = f3(1, 1, 1);
@@ -138,8 +143,8 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
                 active = generate_ray(sc, id, a.rays_per_pixel, a.gen_seed, a.pcg_inc, o, d);
             } else {
                 const uint32_t slot = a.order ? __ldg(a.order + i) : i;
-                const float4 ra = a.in.qa[slot], rb = a.in.qb[slot];
-                const float2 rc = a.in.qc[slot];
+                const float4 ra = __ldcs(a.in.qa + slot), rb = __ldcs(a.in.qb + slot);
+                const float2 rc = __ldcs(a.in.qc + slot);
                 o = f3(ra.x, ra.y, ra.z);
                 d = f3(ra.w, rb.x, rb.y);
                 T = f3(rb.z, rb.w, rc.x);
@@ -150,7 +155,7 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
         float3 radiance = f3(0, 0, 0);
         uint32_t pixel = 0xFFFFFFFFu;
         if (active) {
-            const float2 h = a.hits[i];
+            const float2 h = __ldcs(a.hits + i);
             const float closest = h.x;
             const int prim = __float_as_int(h.y);
             pixel = id / (uint32_t)a.rays_per_pixel;
@@ -163,19 +168,29 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
             }
         }
         add_radiance_warp(a.framebuffer, pixel, radiance);
-        if (write_out) {  // next-bounce compaction: one atomic per warp, survivors stay contiguous
+        if (write_out) {  // next-bounce compaction: survivors keep their order inside the CTA's contiguous output range
             const uint32_t mask = __ballot_sync(0xffffffffu, alive);
-            if (mask) {
-                uint32_t pos = 0;
-                if (lane == 0) pos = atomicAdd(out_count, (uint32_t)__popc(mask));
-                pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(mask & lanemask_lt());
-                if (alive) {
-                    a.out.qa[pos] = make_float4(o.x, o.y, o.z, d.x);
-                    a.out.qb[pos] = make_float4(d.y, d.z, T.x, T.y);
-                    a.out.qc[pos] = make_float2(T.z, __uint_as_float(id));
-                    if (a.keys_out) a.keys_out[pos] = reorder_key(sc.key_min, sc.key_inv_extent, o, d, a.key_bits);
+            if (lane == 0) warp_count[warp] = __popc(mask);
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                uint32_t total = 0;
+#pragma unroll
+                for (int w = 0; w < kShadeBlock / 32; w++) {
+                    const uint32_t c = warp_count[w];
+                    warp_count[w] = total;
+                    total += c;
                 }
+                block_base = total ? atomicAdd(out_count, total) : 0u;
             }
+            __syncthreads();
+            if (alive) {
+                const uint32_t pos = block_base + warp_count[warp] + __popc(mask & lanemask_lt());
+                __stcs(a.out.qa + pos, make_float4(o.x, o.y, o.z, d.x));
+                __stcs(a.out.qb + pos, make_float4(d.y, d.z, T.x, T.y));
+                __stcs(a.out.qc + pos, make_float2(T.z, __uint_as_float(id)));
+                if (a.keys_out) a.keys_out[pos] = reorder_key(sc.key_min, sc.key_inv_extent, o, d, a.key_bits);
+            }
+            __syncthreads();  // warp_count / block_base are rewritten by the next iteration
         }
     }
 }

@@ -42,8 +42,8 @@ struct rt_ctx {
     RayQueue queue[2] = {};
     float2 *d_hits = nullptr;  // {t, prim} per queue position of the bounce in flight
     size_t queue_capacity = 0;
-    int stack_mode = 0;        // 0 = shared-memory traversal stack, 1 = local-memory stack (RT_STACK=local)
-    uint32_t trace_batch = kBatch, trace_refill_below = kRefillBelow;  // RT_BATCH / RT_REFILL override
+    int stack_mode = 1;        // 1 = local-memory traversal stack (default: +5 %, leaves the L1 to the BVH), 0 = shared memory (RT_STACK=smem)
+    uint32_t trace_batch = kBatch, trace_refill_below = kRefillBelow, trace_node_min = kNodeMin;  // RT_BATCH / RT_REFILL override
     uint32_t *d_keys[2] = {nullptr, nullptr}, *d_vals[2] = {nullptr, nullptr};
     size_t sort_capacity = 0;
     uint32_t *d_sort_scratch = nullptr;  // hist + tile counters + tile status
@@ -221,6 +221,7 @@ extern "C" int rt_create(rt_ctx **out, int device)
     RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     if (const char *e = std::getenv("RT_STACK")) ctx->stack_mode = std::strcmp(e, "local") == 0 ? 1 : 0;
     if (const char *e = std::getenv("RT_BATCH")) ctx->trace_batch = (uint32_t)std::min(4096, std::max(4, std::atoi(e)));
+    if (const char *e = std::getenv("RT_NODEMIN")) ctx->trace_node_min = (uint32_t)std::min(33, std::max(0, std::atoi(e)));
     if (const char *e = std::getenv("RT_REFILL")) ctx->trace_refill_below = (uint32_t)std::min(33, std::max(1, std::atoi(e)));
     RT_CUDA(ctx, cudaEventCreate(&ctx->ev_start));
     RT_CUDA(ctx, cudaEventCreate(&ctx->ev_stop));
@@ -535,6 +536,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             a.stack_depth = std::max(4, ctx->packed_depth);
             a.trace_batch = ctx->trace_batch;
             a.trace_refill_below = ctx->trace_refill_below;
+            a.trace_node_min = ctx->trace_node_min;
             // the live count of bounce b > 0 exists only on the device: size the grids for the pass's upper bound
             const int shade_grid = (int)std::min<size_t>((size_t)shade_grid_max, ((size_t)total + kShadeBlock - 1) / kShadeBlock);
             const int t_grid = (int)std::min<size_t>((size_t)grid, ((size_t)total + kBlock - 1) / kBlock);
@@ -683,7 +685,7 @@ extern "C" int rt_trace_closest(rt_ctx *ctx, const float *rays6, int32_t n, int3
         const size_t smem = stack_bytes(ctx);
         const int depth = std::max(4, ctx->packed_depth);
         uint32_t *cursor = &ctx->d_pc->cursor[0];
-        const TraceTuning tune{ctx->trace_batch, ctx->trace_refill_below};
+        const TraceTuning tune{ctx->trace_batch, ctx->trace_refill_below, ctx->trace_node_min};
         const float *r6 = (const float *)rays.p;
         if (ctx->stack_mode) {
             if (stats) trace_kernel<true, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->ds, r6, (uint32_t)n, with_spheres, (int *)prim.p, (float *)t.p, cursor, depth, tune, ctx->d_totals);

@@ -21,23 +21,28 @@ struct TraceCounters {
     uint32_t triangle_tests = 0;
 };
 
-// Boundary-safe slab test (Tavian Barnes' min/max form, scene.cu:109-132): tmin starts at 0, tmax at `limit`.
-// Arithmetic is (bound - o) * inv exactly as the reference writes it; there is no a*b+c shape to contract.
+// Slab test with the reference's boundary-safe semantics (Tavian Barnes' form, scene.cu:109-132: tmin starts at 0,
+// tmax at `limit`, a NaN from 0 * inf leaves the running interval untouched) restated so that it costs 11 ALU-pipe
+// instructions per box instead of 19: the reference evaluates min(max(t1,tmin), max(t2,tmin)) per axis; for non-NaN
+// inputs that is max(min(t1,t2), tmin), and min(t1,t2) is t of the bound the ray meets first, which the SIGN of the
+// direction picks ahead of time (rounding is monotonic, so (lo-o)*inv <= (hi-o)*inv whenever inv >= 0). fmaxf/fminf
+// drop a NaN operand exactly as the reference's chain does, and the three-operand forms compile to FMNMX3.
+// Arithmetic per bound is (bound - o) * inv as the reference writes it; there is no a*b+c shape to contract.
+struct RaySigns {
+    bool x, y, z;  // direction component negative (including -0: 1/-0 = -inf)
+};
+__device__ __forceinline__ RaySigns ray_signs(float3 inv) { return RaySigns{signbit(inv.x) != 0, signbit(inv.y) != 0, signbit(inv.z) != 0}; }
+
 __device__ __forceinline__ bool slab(float lox, float loy, float loz, float hix, float hiy, float hiz, float3 o, float3 inv,
-                                     float limit, float &t_enter)
+                                     RaySigns sg, float limit, float &t_enter)
 {
-    float tmin = 0.0f, tmax = limit;
-    float t1 = (lox - o.x) * inv.x, t2 = (hix - o.x) * inv.x;
-    tmin = fminf(fmaxf(t1, tmin), fmaxf(t2, tmin));
-    tmax = fmaxf(fminf(t1, tmax), fminf(t2, tmax));
-    t1 = (loy - o.y) * inv.y; t2 = (hiy - o.y) * inv.y;
-    tmin = fminf(fmaxf(t1, tmin), fmaxf(t2, tmin));
-    tmax = fmaxf(fminf(t1, tmax), fminf(t2, tmax));
-    t1 = (loz - o.z) * inv.z; t2 = (hiz - o.z) * inv.z;
-    tmin = fminf(fmaxf(t1, tmin), fmaxf(t2, tmin));
-    tmax = fmaxf(fminf(t1, tmax), fminf(t2, tmax));
-    t_enter = tmin;
-    return tmin <= tmax;
+    const float nx = sg.x ? hix : lox, fx = sg.x ? lox : hix;
+    const float ny = sg.y ? hiy : loy, fy = sg.y ? loy : hiy;
+    const float nz = sg.z ? hiz : loz, fz = sg.z ? loz : hiz;
+    const float tn = fmaxf(fmaxf((nx - o.x) * inv.x, (ny - o.y) * inv.y), fmaxf((nz - o.z) * inv.z, 0.0f));
+    const float tf = fminf(fminf((fx - o.x) * inv.x, (fy - o.y) * inv.y), fminf((fz - o.z) * inv.z, limit));
+    t_enter = tn;
+    return tn <= tf;
 }
 
 // scene.cu:338-372. Returns through closest/prim; runs before the BVH and seeds `closest`.
@@ -86,6 +91,7 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
                                              SharedStack<BLOCK> &stack, TraceCounters &ctr)
 {
     const float3 inv = f3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    const RaySigns sg = ray_signs(inv);
     const float4 *__restrict__ nodes = sc.nodes;
     const int lane = threadIdx.x;
     uint32_t cur = 0;  // record 0 is the root
@@ -97,8 +103,8 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
             uint4 q3 = __ldg(reinterpret_cast<const uint4 *>(n + 3));
             if (STATS) ctr.internal_visits++;
             float d0, d1;
-            bool h0 = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv, closest, d0);
-            bool h1 = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv, closest, d1);
+            bool h0 = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv, sg, closest, d0);
+            bool h1 = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv, sg, closest, d1);
             if (h0 && h1) {
                 bool zero_near = d0 < d1;
                 uint32_t far_ref = zero_near ? q3.y : q3.x;
@@ -141,9 +147,11 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
 constexpr uint32_t kDoneRef = 0xFFFFFFFFu;  // never a valid leaf ref: start would exceed the 2^27 triangle limit
 constexpr int kBatch = 96;                  // default: rays a warp claims per global atomic
 constexpr int kRefillBelow = 22;            // default: refill when fewer lanes than this still hold a ray
+constexpr int kNodeMin = 8;                 // default for TraceTuning::node_min
 struct TraceTuning {
     uint32_t batch;         // rays per claim; the kernel shrinks it when the bounce has fewer rays than batch x warps
     uint32_t refill_below;
+    uint32_t node_min;      // leave the descent loop when fewer lanes than this are still descending
 };
 
 // Stack storage policies. Both are entry-major per warp so the 32 lanes of an access hit 32 banks / one 128-byte line.
@@ -176,6 +184,7 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
     const uint32_t warps = gridDim.x * (blockDim.x >> 5);
     const uint32_t batch = max(4u, min(tune.batch, (n + warps - 1) / warps));
     const uint32_t refill_below = tune.refill_below;
+    const uint32_t node_min = tune.node_min;
     uint32_t pool_next = 0, pool_end = 0;  // warp-uniform: unclaimed part of the current batch
     bool exhausted = false;                // warp-uniform: the global cursor ran past n
     bool busy = false;
@@ -183,6 +192,7 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
     int sp = 0, prim = -1;
     float closest = kMissT;
     float3 o = f3(0, 0, 0), d = f3(0, 0, 1), inv = f3(0, 0, 1);
+    RaySigns sg{false, false, false};
 
     for (;;) {
         // ---- refill: all 32 lanes are here ----
@@ -205,6 +215,7 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
                 prim = -1;
                 if (io.load(slot, o, d, closest, prim)) {
                     inv = f3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+                    sg = ray_signs(inv);
                     cur = 0;  // record 0 is the root
                     sp = 0;
                     busy = true;
@@ -230,8 +241,8 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
                 const uint4 q3 = __ldg(reinterpret_cast<const uint4 *>(nd + 3));
                 if (STATS) ctr.internal_visits++;
                 float d0, d1;
-                const bool h0 = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv, closest, d0);
-                const bool h1 = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv, closest, d1);
+                const bool h0 = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv, sg, closest, d0);
+                const bool h1 = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv, sg, closest, d1);
                 if (h0 && h1) {
                     const bool zero_near = d0 < d1;
                     stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
@@ -249,8 +260,10 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
                         stack.get(sp, cur, entry);
                     } while (entry >= closest);
                 }
+                // lanes that already hold a leaf wait at the loop exit: stop descending once only a few are left
+                if (__popc(__activemask()) < node_min) break;
             }
-            if (cur != kDoneRef) {
+            if ((cur & kLeafBit) && cur != kDoneRef) {
                 const uint32_t first = cur & kLeafStartMask;
                 const uint32_t count = (cur >> kLeafCountShift) & 15u;
                 if (STATS) ctr.triangle_tests += count;
