@@ -48,7 +48,8 @@ class SceneDesc(C.Structure):
 
 class RenderOpts(C.Structure):
     _fields_ = [("sort", C.c_int32), ("pass_spp", C.c_int32), ("pass_first", C.c_int32), ("pass_count", C.c_int32),
-                ("collect_stats", C.c_int32), ("stream_id", C.c_int32), ("sort_bits", C.c_int32), ("reserved", C.c_int32)]
+                ("collect_stats", C.c_int32), ("stream_id", C.c_int32), ("sort_bits", C.c_int32), ("pass_group", C.c_int32),
+                ("reserved", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -237,26 +238,26 @@ class Renderer:
         return self
 
     @staticmethod
-    def _opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing=False):
+    def _opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing=False, pass_group=0):
         return RenderOpts(1 if sort else 0, pass_spp, pass_first, pass_count, 1 if collect_stats else 0, stream_id, sort_bits,
-                          1 if timing else 0)
+                          pass_group, 1 if timing else 0)
 
     def render(self, sort=True, out=None, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0,
-               timing=False):
+               timing=False, pass_group=0):
         """rt_render: host output (float32[H,W,3] un-normalised sums). ``out`` may be a preallocated (pinned) array."""
         if out is None:
             out = np.empty((self.height, self.width, 3), np.float32)
         assert out.dtype == np.float32 and out.size == self.width * self.height * 3 and out.flags.c_contiguous
-        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing)
+        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group)
         st = Stats()
         _check(lib().rt_render(self._ctx, C.byref(o), out.ctypes.data, C.byref(st)), self._ctx)
         self.last_stats = st
         return out
 
     def render_device(self, sort=True, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0,
-                      timing=False):
+                      timing=False, pass_group=0):
         """rt_render_device: returns the device pointer (int) of the float32[H*W*3] framebuffer."""
-        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing)
+        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group)
         st = Stats()
         ptr = C.c_void_p()
         _check(lib().rt_render_device(self._ctx, C.byref(o), C.byref(ptr), C.byref(st)), self._ctx)

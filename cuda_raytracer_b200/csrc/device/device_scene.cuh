@@ -11,7 +11,10 @@
 //    bits[26:0] = first triangle. Larger leaves (no_bvh, SAH refusals) are split into chains of same-box records
 //    by the packer. An absent child has a far-away degenerate box (an inverted box would pass the
 //    order-agnostic slab test) and ref = kEmptyRef.
-//  * Triangles: 3 x float4 = {p1 | n.x}, {e1 | n.y}, {e2 | n.z} (precomputed-edge form, scene.cuh:15-33), BVH order.
+//  * Triangles: one 64-byte record (32-byte aligned for LDG.256), BVH order, precomputed-edge form (scene.cuh:15-33):
+//      words 0-7  = p1.xyz, e1.xyz, e2.xy      <- the intersection test reads these 32 bytes + word 8
+//      words 8-12 = e2.z, n.xyz, material index (as int bits)   <- shading reads words 9-12 with one load
+//      words 13-15 unused.
 //  * Materials: 3 x float4, the reference's 48-byte record. Spheres: float4. Environment map: float4 texels.
 //  * Ray queues: SoA, 40 bytes per live ray:
 //      qa = {o.x, o.y, o.z, d.x}   qb = {d.y, d.z, T.r, T.g}   qc = {T.b, ray id (bits)}
@@ -28,6 +31,7 @@ constexpr uint32_t kEmptyRef = 0x80000000u;  // leaf with zero triangles; its bo
 constexpr int kLeafCountShift = 27;
 constexpr uint32_t kLeafStartMask = (1u << kLeafCountShift) - 1u;
 constexpr int kMaxLeafTris = 15;
+constexpr int kMaxPassGroup = 16;  // passes traced together as one wave (rt_render_opts.pass_group)
 constexpr int kStackDepth = 32;  // per-thread traversal stack entries in shared memory
 
 // accept t iff t > kTMin: the reference rejects `t < 0.005` in DOUBLE (scene.cu:190,357,366); 0.005f is the largest
@@ -37,7 +41,7 @@ constexpr float kMissT = 1e30f;
 
 struct DeviceScene {
     const float4 *nodes;      // 4 per internal record
-    const float4 *tris;       // 3 per triangle
+    const float4 *tris;       // 4 per triangle (64-byte records)
     const float4 *materials;  // 3 per material
     const float4 *spheres;
     const float4 *env;
@@ -77,11 +81,12 @@ struct BounceArgs {
     PassCounters *pc;
     RenderTotals *totals;
     float *framebuffer;     // 3 floats per pixel, un-normalised sums
-    uint32_t n_first;       // rays in the pass (bounce 0 only)
+    uint32_t n_first;       // rays of the wave = group x pass_rays (bounce 0 only)
+    uint32_t pass_rays;     // rays of ONE pass (pixels x rays_per_pixel); ray id = pass-in-wave x pass_rays + index in pass
     int32_t bounce;
-    int32_t rays_per_pixel; // of this pass
-    uint32_t gen_seed;      // 709579 * remaining_rays          (scene.cu:81)
-    uint32_t proc_seed;     // 279220567 * (remaining*20+bounce) (raytracing.cu:89,236)
+    int32_t rays_per_pixel; // of every pass of this wave
+    uint32_t gen_seed[kMaxPassGroup];   // per pass of the wave: 709579 * remaining_rays           (scene.cu:81)
+    uint32_t proc_seed[kMaxPassGroup];  // per pass of the wave: 279220567 * (remaining*20+bounce)  (raytracing.cu:89,236)
     unsigned long long pcg_inc;  // 820957824423429 | 1 for stream 0 (random.cuh:28)
     int32_t key_bits;
     uint32_t trace_batch, trace_refill_below, trace_node_min;  // TraceTuning

@@ -63,7 +63,8 @@ struct QueueTraceIO {
     __device__ __forceinline__ bool load(uint32_t i, float3 &o, float3 &d, float &closest, int &prim) const
     {
         if (FIRST) {
-            if (!generate_ray(sc, i, a.rays_per_pixel, a.gen_seed, a.pcg_inc, o, d)) return false;
+            const uint32_t g = i / a.pass_rays;  // pass of the wave; seeds and pixel follow the index inside that pass
+            if (!generate_ray(sc, i - g * a.pass_rays, a.rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d)) return false;
         } else {
             const uint32_t slot = a.order ? __ldg(a.order + i) : i;
             const float4 ra = __ldcs(a.in.qa + slot), rb = __ldcs(a.in.qb + slot);
@@ -140,7 +141,8 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
         uint32_t id = i;
         if (active) {
             if (FIRST) {
-                active = generate_ray(sc, id, a.rays_per_pixel, a.gen_seed, a.pcg_inc, o, d);
+                const uint32_t g = id / a.pass_rays;
+                active = generate_ray(sc, id - g * a.pass_rays, a.rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d);
             } else {
                 const uint32_t slot = a.order ? __ldg(a.order + i) : i;
                 const float4 ra = __ldcs(a.in.qa + slot), rb = __ldcs(a.in.qb + slot);
@@ -158,11 +160,12 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
             const float2 h = __ldcs(a.hits + i);
             const float closest = h.x;
             const int prim = __float_as_int(h.y);
-            pixel = id / (uint32_t)a.rays_per_pixel;
+            const uint32_t g = id / a.pass_rays, index = id - g * a.pass_rays;  // pass of the wave, ray index inside it
+            pixel = index / (uint32_t)a.rays_per_pixel;
             if (prim < 0) {
                 radiance = shade_miss(sc, d) * T;
             } else {
-                Pcg rng = pcg_seed(id * 4137874753u + a.proc_seed, a.pcg_inc);  // raytracing.cu:89 with slot == ray id
+                Pcg rng = pcg_seed(index * 4137874753u + a.proc_seed[g], a.pcg_inc);  // raytracing.cu:89 with slot == ray index
                 shade_hit(sc, o, d, closest, prim, T, rng, radiance);
                 alive = !is_zero(T);  // a path dies only when its throughput is exactly zero (Q10)
             }

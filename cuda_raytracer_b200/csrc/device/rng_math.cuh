@@ -29,6 +29,20 @@ __device__ __forceinline__ float dot_nofma(float3 a, float3 b)
     return __fadd_rn(__fadd_rn(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y)), __fmul_rn(a.z, b.z));
 }
 
+// 256-bit read-only load (sm_100a: LDG.E.256): one L1 request for half a BVH record / a triangle's edge block where the
+// 128-bit form needs two. p must be 32-byte aligned.
+struct __align__(32) Float8 {
+    float4 lo, hi;
+};
+__device__ __forceinline__ Float8 ldg256(const void *p)
+{
+    Float8 r;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r.lo.x), "=f"(r.lo.y), "=f"(r.lo.z), "=f"(r.lo.w), "=f"(r.hi.x), "=f"(r.hi.y), "=f"(r.hi.z), "=f"(r.hi.w)
+                 : "l"(p));
+    return r;
+}
+
 struct Pcg {
     unsigned long long state;
     unsigned long long inc;  // already OR-ed with 1

@@ -279,15 +279,14 @@ extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *s)
     ctx->packed_nodes = (int)packer.out.size();
     ctx->packed_depth = packer.max_depth;
 
-    // triangles: {p1|n.x} {e1|n.y} {e2|n.z}
-    std::vector<float> tri4((size_t)s->triangle_count * 12);
+    // triangles: 64-byte records {p1, e1, e2.xy | e2.z, n, material index, pad} (device_scene.cuh)
+    std::vector<float> tri4((size_t)s->triangle_count * 16, 0.0f);
     for (int i = 0; i < s->triangle_count; i++) {
-        const float *t = s->triangles + 12 * (size_t)i;
-        float *o = &tri4[12 * (size_t)i];
-        for (int k = 0; k < 3; k++) {
-            o[4 * k + 0] = t[3 * k + 0]; o[4 * k + 1] = t[3 * k + 1]; o[4 * k + 2] = t[3 * k + 2];
-            o[4 * k + 3] = t[9 + k];
-        }
+        const float *t = s->triangles + 12 * (size_t)i;  // p1, e1, e2, n
+        float *o = &tri4[16 * (size_t)i];
+        for (int k = 0; k < 12; k++) o[k] = t[k];
+        const uint32_t mat = s->material_indices[s->sphere_count + i];
+        std::memcpy(&o[12], &mat, sizeof(mat));
     }
     size_t texels = (size_t)s->env_width * s->env_height;
     std::vector<float> env4(texels * 4);
@@ -495,7 +494,18 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     RT_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = ensure_framebuffer(ctx);
     if (rc != RT_OK) return rc;
-    if ((rc = ensure_queues(ctx, pixels * (size_t)std::min(pass_spp, std::max(1, ctx->ray_count)), sort)) != RT_OK) return rc;
+    const size_t pass_rays_max = pixels * (size_t)std::min(pass_spp, std::max(1, ctx->ray_count));
+    int max_group = opts.pass_group;
+    if (max_group <= 0) {  // auto: as many passes per wave as fit in a third of the free device memory (ids stay < 2^31)
+        size_t free_b = 0, total_b = 0;
+        RT_CUDA(ctx, cudaMemGetInfo(&free_b, &total_b));
+        const size_t have = ctx->queue_capacity * (size_t)(88 + (sort ? 16 : 0));  // already ours, so also "free"
+        const size_t per_pass = pass_rays_max * (size_t)(88 + (sort ? 16 : 0));    // 2 x 40 B queues + 8 B hit (+ keys, permutation)
+        max_group = (int)std::max<size_t>(1, (free_b + have) / 3 / std::max<size_t>(1, per_pass));
+    }
+    max_group = std::max(1, std::min({max_group, (int)kMaxPassGroup, pass_end - pass_first}));
+    while (max_group > 1 && pass_rays_max * (size_t)max_group >= (1ull << 31)) max_group--;
+    if ((rc = ensure_queues(ctx, pass_rays_max * (size_t)max_group, sort)) != RT_OK) return rc;
 
     int grid = 0;
     if ((rc = trace_grid_size(ctx, &grid)) != RT_OK) return rc;
@@ -507,11 +517,18 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
 
     int launches = 0, passes_done = 0;
     long long primaries = 0;
-    for (int pass = pass_first; pass < pass_end; pass++) {
-        const int before = ctx->ray_count - pass * pass_spp;
-        const int rays_to_cast = std::min(before, pass_spp);
-        const int remaining = before - rays_to_cast;  // the reference's `remaining_rays` after the decrement (:224-225)
-        const uint32_t total = (uint32_t)(pixels * (size_t)rays_to_cast);
+    // A WAVE is `group` consecutive passes of equal size traced together: every pass keeps the reference's seeds
+    // (they depend on the pass, not on the launch), while the late bounces - a few 10^4 rays per pass, latency-bound -
+    // and the launch gaps are paid once per wave instead of once per pass.
+    for (int pass = pass_first; pass < pass_end;) {
+        const int rays_to_cast = std::min(ctx->ray_count - pass * pass_spp, pass_spp);
+        const uint32_t pass_rays = (uint32_t)(pixels * (size_t)rays_to_cast);
+        int group = 1;
+        while (group < max_group && pass + group < pass_end && std::min(ctx->ray_count - (pass + group) * pass_spp, pass_spp) == rays_to_cast)
+            group++;
+        int remaining[kMaxPassGroup];  // the reference's `remaining_rays` after the decrement (:224-225), per pass
+        for (int g = 0; g < group; g++) remaining[g] = ctx->ray_count - (pass + g) * pass_spp - rays_to_cast;
+        const uint32_t total = pass_rays * (uint32_t)group;
         primaries += total;
         RT_CUDA(ctx, cudaMemsetAsync(ctx->d_pc, 0, sizeof(PassCounters), ctx->stream));
         const uint32_t *order = nullptr;
@@ -526,10 +543,13 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             a.totals = ctx->d_totals;
             a.framebuffer = ctx->d_fb;
             a.n_first = total;
+            a.pass_rays = pass_rays;
             a.bounce = b;
             a.rays_per_pixel = rays_to_cast;
-            a.gen_seed = 709579u * (uint32_t)remaining;                                // scene.cu:81
-            a.proc_seed = 279220567u * (uint32_t)(remaining * 20 + b);                 // raytracing.cu:89,236
+            for (int g = 0; g < group; g++) {
+                a.gen_seed[g] = 709579u * (uint32_t)remaining[g];                      // scene.cu:81
+                a.proc_seed[g] = 279220567u * (uint32_t)(remaining[g] * 20 + b);       // raytracing.cu:89,236
+            }
             a.pcg_inc = pcg_inc;
             a.key_bits = key_bits;
             a.hits = ctx->d_hits;
@@ -558,7 +578,8 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
                 order = sv;
             }
         }
-        passes_done++;
+        passes_done += group;
+        pass += group;
     }
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
     RT_CUDA(ctx, cudaGetLastError());

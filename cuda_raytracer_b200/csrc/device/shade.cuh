@@ -72,14 +72,17 @@ __device__ __forceinline__ void shade_hit(const DeviceScene &sc, float3 &o, floa
 {
     float3 hit = o + t * d;
     float3 n;
+    uint32_t material;
     if (prim < sc.sphere_count) {
         float4 s = __ldg(sc.spheres + prim);
         n = (1.0f / s.w) * (hit - f3(s.x, s.y, s.z));
-    } else {
-        const float4 *t4 = sc.tris + 3 * (size_t)(prim - sc.sphere_count);
-        n = f3(__ldg(t4).w, __ldg(t4 + 1).w, __ldg(t4 + 2).w);
+        material = __ldg(sc.material_indices + prim);
+    } else {  // words 8-15 of the triangle record: e2.z, n.xyz, material index
+        const Float8 t8 = ldg256(sc.tris + 4 * (size_t)(prim - sc.sphere_count) + 2);
+        n = f3(t8.lo.y, t8.lo.z, t8.lo.w);
+        material = __float_as_uint(t8.hi.x);
     }
-    const float4 *m = sc.materials + 3 * (size_t)__ldg(sc.material_indices + prim);
+    const float4 *m = sc.materials + 3 * (size_t)material;
     float4 m0 = __ldg(m), m1 = __ldg(m + 1), m2 = __ldg(m + 2);
     float3 diffuse = f3(m0.x, m0.y, m0.z), specular = f3(m1.x, m1.y, m1.z);
     float metallicity = m0.w, roughness = m1.w, ior = m2.w;

@@ -67,9 +67,10 @@ __device__ __forceinline__ void intersect_spheres(const DeviceScene &sc, float3 
 __device__ __forceinline__ void intersect_triangle(const float4 *__restrict__ tris, uint32_t tri, int prim_base, float3 o, float3 d,
                                                    float &closest, int &prim)
 {
-    const float4 *t4 = tris + 3 * (size_t)tri;
-    float4 a4 = __ldg(t4), b4 = __ldg(t4 + 1), c4 = __ldg(t4 + 2);
-    float3 p1 = f3(a4.x, a4.y, a4.z), e1 = f3(b4.x, b4.y, b4.z), e2 = f3(c4.x, c4.y, c4.z);
+    const float4 *t4 = tris + 4 * (size_t)tri;
+    const Float8 t8 = ldg256(t4);
+    const float e2z = __ldg(reinterpret_cast<const float *>(t4 + 2));
+    float3 p1 = f3(t8.lo.x, t8.lo.y, t8.lo.z), e1 = f3(t8.lo.w, t8.hi.x, t8.hi.y), e2 = f3(t8.hi.z, t8.hi.w, e2z);
     float3 h = cross(d, e2);
     float a = dot(h, e1);
     if (a == 0.0f) return;
@@ -99,8 +100,9 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
     for (;;) {
         if (!(cur & kLeafBit)) {
             const float4 *n = nodes + 4 * (size_t)cur;
-            float4 q0 = __ldg(n), q1 = __ldg(n + 1), q2 = __ldg(n + 2);
-            uint4 q3 = __ldg(reinterpret_cast<const uint4 *>(n + 3));
+            const Float8 na = ldg256(n), nb = ldg256(n + 2);
+            const float4 q0 = na.lo, q1 = na.hi, q2 = nb.lo;
+            const uint2 q3 = make_uint2(__float_as_uint(nb.hi.x), __float_as_uint(nb.hi.y));
             if (STATS) ctr.internal_visits++;
             float d0, d1;
             bool h0 = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv, sg, closest, d0);
@@ -237,8 +239,9 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
             // descend through internal records until this lane holds a leaf (or runs dry)
             while (!(cur & kLeafBit)) {
                 const float4 *nd = nodes + 4 * (size_t)cur;
-                const float4 q0 = __ldg(nd), q1 = __ldg(nd + 1), q2 = __ldg(nd + 2);
-                const uint4 q3 = __ldg(reinterpret_cast<const uint4 *>(nd + 3));
+                const Float8 na = ldg256(nd), nb = ldg256(nd + 2);
+                const float4 q0 = na.lo, q1 = na.hi, q2 = nb.lo;
+                const uint2 q3 = make_uint2(__float_as_uint(nb.hi.x), __float_as_uint(nb.hi.y));
                 if (STATS) ctr.internal_visits++;
                 float d0, d1;
                 const bool h0 = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv, sg, closest, d0);

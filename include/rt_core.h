@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RT_API_VERSION 2
+#define RT_API_VERSION 3
 
 typedef enum rt_status {
     RT_OK = 0,
@@ -75,6 +75,8 @@ typedef struct rt_render_opts {
                               k > 0 = disjoint PCG streams: stream k's `inc` differs (random.cuh:28), for multi-GPU runs
                               that do NOT want pass-identical images */
     int32_t sort_bits;     /* key width for the reorder pass, 0 = default */
+    int32_t pass_group;    /* passes traced together as one wave: 0 = auto (memory budget, at most 16), 1 = one pass per wave as the
+                              reference does. Results do not depend on it beyond float summation order. */
     int32_t reserved;      /* bit 0: time every bounce kernel / reorder pass with CUDA events (rt_stats.trace_ms, shade_ms, sort_ms) */
 } rt_render_opts;
 

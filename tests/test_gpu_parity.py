@@ -172,6 +172,22 @@ def test_pass_split_sums_to_whole(renderer):
     assert renderer.last_stats.passes == 1
 
 
+def test_pass_grouping_does_not_change_the_image(renderer):
+    """Waves of several passes (rt_render_opts.pass_group) keep every pass's own seeds: same image as one pass per
+    wave up to float summation order, same ray counts; the ragged last pass forms its own wave."""
+    _setup(renderer, "cornell_plus", 48, 40, 110, 6)  # 6 passes: 5 x 20 + 10
+    one = renderer.render(sort=False, pass_group=1)
+    n_one = renderer.last_stats.live_ray_bounces
+    for group, sort in ((0, False), (2, False), (4, True), (16, False)):
+        img = renderer.render(sort=sort, pass_group=group)
+        st = renderer.last_stats
+        assert st.live_ray_bounces == n_one and st.passes == 6 and st.primary_rays == 48 * 40 * 110
+        assert np.allclose(img, one, rtol=1e-4, atol=1e-4 * one.mean())
+    part = renderer.render(sort=False, pass_group=3, pass_first=1, pass_count=4)
+    ref = renderer.render(sort=False, pass_group=1, pass_first=1, pass_count=4)
+    assert np.allclose(part, ref, rtol=1e-4, atol=1e-4 * ref.mean())
+
+
 def test_edge_configs(renderer):
     _setup(renderer, "cornell", 33, 17, 1, 1)  # ragged size, one sample, one bounce: only emitters seen directly
     img = renderer.render(sort=True)

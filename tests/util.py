@@ -88,3 +88,49 @@ def tonemap8(img_sum, exposure, ray_count):
     po.port().oracle_tonemap(np.ascontiguousarray(img_sum, np.float32).reshape(-1), img_sum.shape[0] * img_sum.shape[1],
                              float(exposure), int(ray_count), out.reshape(-1))
     return out
+
+
+def read_png_rgb8(path):
+    """Minimal PNG reader (8-bit RGB, non-interlaced; all five filter types) -> uint8[H, W, 3]. Enough for the files
+    stb_image_write and rt_write_png produce; keeps the tests free of imaging dependencies."""
+    import struct
+    import zlib
+    data = open(path, "rb").read()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    pos, idat, w = 8, b"", None
+    while pos < len(data):
+        n, kind = struct.unpack(">I4s", data[pos:pos + 8])
+        body = data[pos + 8:pos + 8 + n]
+        if kind == b"IHDR":
+            w, h, depth, ctype, _, _, interlace = struct.unpack(">IIBBBBB", body)
+            assert depth == 8 and ctype == 2 and interlace == 0
+        elif kind == b"IDAT":
+            idat += body
+        pos += 12 + n
+    raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(h, 1 + 3 * w)
+    out = np.zeros((h, 3 * w), np.uint8)
+    prev = np.zeros(3 * w, np.int32)
+    for y in range(h):
+        f, line = int(raw[y, 0]), raw[y, 1:].astype(np.int32)
+        if f == 0:
+            cur = line
+        elif f == 2:
+            cur = (line + prev) & 255
+        else:  # sub / average / paeth depend on the pixel to the left: sequential over x, vectorised over the 3 channels
+            cur = np.zeros(3 * w, np.int32)
+            for x in range(0, 3 * w, 3):
+                a = cur[x - 3:x] if x else np.zeros(3, np.int32)
+                b = prev[x:x + 3]
+                c = prev[x - 3:x] if x else np.zeros(3, np.int32)
+                if f == 1:
+                    pred = a
+                elif f == 3:
+                    pred = (a + b) >> 1
+                else:
+                    p = a + b - c
+                    pa, pb, pc = np.abs(p - a), np.abs(p - b), np.abs(p - c)
+                    pred = np.where((pa <= pb) & (pa <= pc), a, np.where(pb <= pc, b, c))
+                cur[x:x + 3] = (line[x:x + 3] + pred) & 255
+        out[y] = cur
+        prev = cur
+    return out.reshape(h, w, 3)

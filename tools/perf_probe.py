@@ -19,7 +19,8 @@ n_int = st.internal_visits / st.live_ray_bounces; n_tri = st.triangle_tests / st
 print(f"{name} {w}x{h}x{spp}x{bounces}: N_int {n_int:.2f} N_tri {n_tri:.2f} bytes/ray-bounce {104+64*n_int+48*n_tri:.0f} live/primary {st.live_ray_bounces/st.primary_rays:.3f}")
 print(" live per bounce (1 pass):", [int(v) for v in st.live_per_bounce[:bounces]])
 for v in variants:
-    kw = dict(sort=v != "nosort", sort_bits=int(v[4:]) if v.startswith("sort") else 0)
+    kw = dict(sort=v.startswith("sort"), sort_bits=int(v[4:]) if v.startswith("sort") else 0,
+              pass_group=int(v[5:]) if v.startswith("group") else 1)
     best = None
     for rep in range(3):
         r.render_device(timing=True, **kw)
