@@ -49,6 +49,7 @@ def parse_args():
     p.add_argument("--workload", default="lamp_4k", choices=sorted(WORKLOADS))
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--sort", type=int, default=0, help="1 = reorder live rays between bounces")
+    p.add_argument("--pass-group", type=int, default=0, help="passes traced together as one wave; 0 = auto, 1 = one pass per wave")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-ref-gpu", action="store_true", help="skip timing the reference's sm_100a GPU binary")
     return p.parse_args()
@@ -98,11 +99,7 @@ def visible_gpu_index(local_rank):
     return local_rank
 
 
-def pass_range(total_passes, rank, world):
-    """Contiguous block of passes for `rank` (passes are the independent unit, raytracing.cu:222-254)."""
-    base, extra = divmod(total_passes, world)
-    first = rank * base + min(rank, extra)
-    return first, base + (1 if rank < extra else 0)
+from cuda_raytracer_b200.multi_gpu import DeviceFramebuffer as _DevBuf, pass_range  # noqa: E402  (host-side split logic, tested on CPU with gloo)
 
 
 # ---- reference arm / cpu_baseline: the reference's own CPU path (oracle/_ref/raytracing_ref cpu no_gpu) -------------
@@ -192,28 +189,29 @@ def reference_arm(args, rank, world):
 
 
 # ---- the B200 arm ------------------------------------------------------------------------------------------------------
-class _DevBuf:
-    """Zero-copy view of the core's device framebuffer for torch (so NCCL can reduce it in place)."""
-
-    def __init__(self, ptr, n):
-        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
-
-
 def ref_gpu_timing(scene, w, h, bounces):
-    """The reference's sm_100a GPU build on the same box: `GPU Took` at two spp values -> steady-state slope."""
-    out = {}
-    lo, hi = (100, 300) if w * h <= 1_000_000 else (40, 120)  # whole passes of 20 spp; a few seconds in total
-    for spp in (lo, hi):
-        path = _scene_file_with_image(scene, w, h, spp, bounces)
-        try:
-            res = {}
-            for flags in ((), ("no_sort",)):
-                o = subprocess.run([REF_BIN, path, *flags], cwd=SCENES, capture_output=True, text=True, timeout=1800).stdout
-                m = re.search(r"GPU Took ([0-9.eE+-]+)s", o)
-                res["no_sort" if flags else "sort"] = float(m.group(1)) if m else None
-            out[spp] = res
-        finally:
-            os.unlink(path)
+    """The reference's sm_100a GPU build on the same box. Its `GPU Took` timer includes allocation, scene upload and the
+    download, so the steady-state rate is the SLOPE between two spp values (whole passes of 20); the first run of each
+    mode is a discarded warm-up (cold CUDA context / page cache), and the points are far apart so that run-to-run noise
+    (~0.05 s) is small against the difference."""
+    lo, hi = (100, 500) if w * h <= 1_000_000 else (40, 200)
+    out = {lo: {}, hi: {}}
+    paths = {spp: _scene_file_with_image(scene, w, h, spp, bounces) for spp in (lo, hi)}
+
+    def took(spp, flags):
+        o = subprocess.run([REF_BIN, paths[spp], *flags], cwd=SCENES, capture_output=True, text=True, timeout=1800).stdout
+        m = re.search(r"GPU Took ([0-9.eE+-]+)s", o)
+        return float(m.group(1)) if m else None
+
+    try:
+        for flags in ((), ("no_sort",)):
+            mode = "no_sort" if flags else "sort"
+            took(lo, flags)  # warm-up, discarded
+            out[lo][mode] = took(lo, flags)
+            out[hi][mode] = took(hi, flags)
+    finally:
+        for pth in paths.values():
+            os.unlink(pth)
     return out
 
 
@@ -257,7 +255,7 @@ def main():
     def frame(timing=False):
         """One step, inputs resident: this rank's passes, then the reduce of the accumulation buffer to rank 0."""
         if count > 0:
-            ptr = r.render_device(sort=sort, pass_first=first, pass_count=count, timing=timing)
+            ptr = r.render_device(sort=sort, pass_first=first, pass_count=count, timing=timing, pass_group=args.pass_group)
             st = r.last_stats
             dev_s, live, launches, tr_ms, sh_ms, so_ms = st.loop_seconds, st.live_ray_bounces, st.kernel_launches, st.trace_ms, st.shade_ms, st.sort_ms
         else:  # more ranks than passes: contribute zeros
@@ -281,9 +279,9 @@ def main():
         t0 = time.perf_counter()
         r.upload(scene)
         if dist is None:
-            r.render(sort=sort, out=host_out.reshape(h, w, 3))
+            r.render(sort=sort, out=host_out.reshape(h, w, 3), pass_group=args.pass_group)
         else:
-            ptr = r.render_device(sort=sort, pass_first=first, pass_count=max(count, 1))
+            ptr = r.render_device(sort=sort, pass_first=first, pass_count=max(count, 1), pass_group=args.pass_group)
             fb = torch.as_tensor(_DevBuf(ptr, n_floats), device=f"cuda:{local_rank}")
             if count == 0:
                 fb.zero_()
@@ -359,7 +357,7 @@ def main():
         "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{scene_name}.scene {w}x{h} {spp} spp {bounces} bounces (lamp-subset geometry, synthetic env map)",
-                   "passes": total_passes, "pass_spp": PASS_SPP, "sort": int(sort), "parallelism": f"spp-split x{world} + NCCL reduce",
+                   "passes": total_passes, "pass_spp": PASS_SPP, "pass_group": args.pass_group or "auto (free memory / 3)", "sort": int(sort), "parallelism": f"spp-split x{world} + NCCL reduce",
                    "l2": "inputs larger than L2: ray queues are %.1f GB per pass; the packed scene (%.0f MB) is L2-resident by nature"
                          % (w * h * PASS_SPP * 40 * 2 / 1e9, scene_bytes / 1e6)},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_s / args.steps * 1e3,

@@ -32,11 +32,11 @@ def _scene_copy(tmp_path, name, w, h, spp, bounces):
     return name + ".scene"
 
 
-def _run(exe, tmp_path, scene, *flags):
+def _run(exe, tmp_path, scene, *flags, png="raytracing.png"):
     r = subprocess.run([exe, scene, *flags], cwd=tmp_path, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
-    img = read_png_rgb8(str(tmp_path / "raytracing.png"))
-    os.remove(tmp_path / "raytracing.png")
+    img = read_png_rgb8(str(tmp_path / png))
+    os.remove(tmp_path / png)
     return img, r.stdout
 
 
@@ -44,14 +44,14 @@ def test_command_line_writes_the_reference_outputs(tmp_path):
     scene = _scene_copy(tmp_path, "teapot", 120, 90, 40, 6)
     img, out = _run(EXE, tmp_path, scene)
     assert img.shape == (90, 120, 3) and img.mean() > 5
-    for line in ("Loaded environment map with size 1024,1024", "Triangle count 126050", "Node count 81311", "BVH Took", "GPU Took"):
+    for line in ("Loaded environment map with size 1024,1024", "Triangle count: 126050", "Node count: 81311", "BVH Took", "GPU Took"):
         assert line in out, out
     img2, out2 = _run(EXE, tmp_path, scene, "no_sort", "no_bvh")
-    assert "Node count 1" in out2
+    assert "Node count: 1\n" in out2
     diff = np.sqrt(np.mean((img.astype(np.float64) - img2.astype(np.float64)) ** 2))
     assert diff < 6.0  # same streams, same geometry: only bloom-threshold flips and float order differ
-    _, out3 = _run(EXE, tmp_path, scene, "stats", "out=custom.png")
-    assert os.path.exists(tmp_path / "custom.png") and '"mrays_per_s"' in out3
+    img3, out3 = _run(EXE, tmp_path, scene, "stats", "out=custom.png", png="custom.png")
+    assert img3.shape == img.shape and '"mrays_per_s"' in out3 and not os.path.exists(tmp_path / "raytracing.png")
 
 
 @pytest.mark.parametrize("name,w,h,spp", [("cornell", 160, 160, 200), ("cornell_plus", 160, 160, 200), ("spheres", 200, 150, 200),
