@@ -361,7 +361,8 @@ def main():
                    "l2": "inputs larger than L2: ray queues are %.1f GB per pass; the packed scene (%.0f MB) is L2-resident by nature"
                          % (w * h * PASS_SPP * 40 * 2 / 1e9, scene_bytes / 1e6)},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_s / args.steps * 1e3,
-                "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(n_floats * 4)},
+                "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(n_floats * 4),
+                "ms_each": [round(t * 1e3, 2) for t in e2e_t]},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
