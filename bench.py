@@ -159,13 +159,13 @@ def size_cpu_sample(scene, w, h, bounces, target_seconds=12.0):
     return spp
 
 
-def reference_arm(args, rank, world):
+def reference_arm(args, rank, world, emit):
     if rank != 0:
         return 0
     scene, w, h, spp, bounces = WORKLOADS[args.workload]
     cfg = {"workload": f"{scene}.scene {w}x{h} {spp} spp {bounces} bounces (lamp-subset geometry, synthetic env map)", "l2": "n/a (CPU)"}
     if not os.path.exists(REF_BIN):
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/raytracing_ref was not built (needs /root/reference at build time)"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/raytracing_ref was not built (needs /root/reference at build time)"})
         return 0
     ratio, threads = live_per_primary(scene, w, h, bounces)
     s_spp = size_cpu_sample(scene, w, h, bounces, 10.0)
@@ -184,7 +184,7 @@ def reference_arm(args, rank, world):
             "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "reference", "sample": sample},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -217,11 +217,21 @@ def ref_gpu_timing(scene, w, h, bounces):
 
 def main():
     args = parse_args()
+    # Libraries (NCCL prints its version banner) may write to stdout; the contract is ONE JSON line there. Keep the real
+    # stdout aside and point fd 1 at stderr for the duration of the run.
+    sys.stdout.flush()
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+    def emit(obj):
+        real_stdout.write(json.dumps(obj) + "\n")
+        real_stdout.flush()
+
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
-        return reference_arm(args, rank, world)
+        return reference_arm(args, rank, world, emit)
 
     import numpy as np
     import torch
@@ -274,10 +284,13 @@ def main():
             red_s = e0.elapsed_time(e1) * 1e-3
         return dev_s + red_s, live, launches, tr_ms, so_ms, red_s, sh_ms
 
+    e2e_upload = []
+
     def frame_e2e():
         """The reference-facing call with host buffers: upload (BVH packing + H2D), render, D2H of the sums."""
         t0 = time.perf_counter()
         r.upload(scene)
+        e2e_upload.append(time.perf_counter() - t0)
         if dist is None:
             r.render(sort=sort, out=host_out.reshape(h, w, 3), pass_group=args.pass_group)
         else:
@@ -362,7 +375,7 @@ def main():
                          % (w * h * PASS_SPP * 40 * 2 / 1e9, scene_bytes / 1e6)},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_s / args.steps * 1e3,
                 "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(n_floats * 4),
-                "ms_each": [round(t * 1e3, 2) for t in e2e_t]},
+                "ms_each": [round(t * 1e3, 2) for t in e2e_t], "upload_ms_each": [round(t * 1e3, 2) for t in e2e_upload[-len(e2e_t):]]},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
@@ -391,7 +404,7 @@ def main():
                 slope = (tg[hi][mode] - tg[lo][mode]) / float(hi - lo)
                 ref[f"{mode}_mrays_per_s_steady"] = lpp * rw * rh / max(slope, 1e-9) * 1e-6
         line["reference_gpu_sm100a"] = ref
-    print(json.dumps(line))
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
     return 0

@@ -165,11 +165,15 @@ struct SmemStack {
     __device__ __forceinline__ void push(int sp, uint32_t r, float d) { ref[sp * BLOCK] = r; dist[sp * BLOCK] = d; }
     __device__ __forceinline__ void get(int sp, uint32_t &r, float &d) const { r = ref[sp * BLOCK]; d = dist[sp * BLOCK]; }
 };
-struct LocalStack {  // thread-local arrays: the hardware interleaves local memory per lane, lines live in L1
-    uint32_t ref[kStackDepth];
-    float dist[kStackDepth];
-    __device__ __forceinline__ void push(int sp, uint32_t r, float d) { ref[sp] = r; dist[sp] = d; }
-    __device__ __forceinline__ void get(int sp, uint32_t &r, float &d) const { r = ref[sp]; d = dist[sp]; }
+struct LocalStack {  // thread-local array: the hardware interleaves local memory per lane, lines live in L1
+    uint2 e[kStackDepth];  // {ref, entry distance bits}: one 64-bit STL / LDL per push / pop
+    __device__ __forceinline__ void push(int sp, uint32_t r, float d) { e[sp] = make_uint2(r, __float_as_uint(d)); }
+    __device__ __forceinline__ void get(int sp, uint32_t &r, float &d) const
+    {
+        const uint2 v = e[sp];
+        r = v.x;
+        d = __uint_as_float(v.y);
+    }
 };
 
 template <bool STATS, class Stack, class IO>
