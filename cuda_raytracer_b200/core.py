@@ -16,7 +16,7 @@ import os
 import numpy as np
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_PKG, "librtcore.so")
+LIB_PATH = os.environ.get("RT_LIBRTCORE") or os.path.join(_PKG, "librtcore.so")  # override = A/B builds of the same ABI
 
 RT_OK = 0
 NODE_DTYPE = np.dtype([("min", np.float32, 3), ("max", np.float32, 3), ("child1", np.int32), ("child2", np.int32)])

@@ -3,10 +3,7 @@
 //  * BVH: only INTERNAL nodes are stored, one 64-byte record (4 x float4, 64-byte aligned) per node holding BOTH
 //    children's boxes and both child references, so one visit = one cache-line-half fetch instead of the
 //    reference's node + two child loads (scene.cu:145-201). Valid because children are always adjacent.
-//      q0 = {c0.min.x, c0.min.y, c0.min.z, c0.max.x}
-//      q1 = {c0.max.y, c0.max.z, c1.min.x, c1.min.y}
-//      q2 = {c1.min.z, c1.max.x, c1.max.y, c1.max.z}
-//      q3 = {ref0, ref1, 0, 0} (as ints)
+//      half 0 = {c0.min.xyz, c0.max.xyz, ref0, pad}   half 1 = {c1.min.xyz, c1.max.xyz, ref1, pad}   (32 bytes each)
 //    ref: bit31 clear -> index of an internal record; bit31 set -> leaf: bits[30:27] = triangle count (1..15),
 //    bits[26:0] = first triangle. Larger leaves (no_bvh, SAH refusals) are split into chains of same-box records
 //    by the packer. An absent child has a far-away degenerate box (an inverted box would pass the

@@ -20,7 +20,10 @@ namespace rtd {
 
 constexpr int kBlock = 128;        // threads per CTA of the traversal kernels
 constexpr int kBlocksPerSM = 6;       // shared-memory stack variant: 6 x 32 KB at full depth
-constexpr int kBlocksPerSMLocal = 8;  // local-memory stack variant: 32 warps per SM, <= 64 registers per thread
+#ifndef RT_TRACE_CTAS
+#define RT_TRACE_CTAS 8
+#endif
+constexpr int kBlocksPerSMLocal = RT_TRACE_CTAS;  // local-memory stack variant: 8 -> 32 warps per SM, <= 64 registers per thread
 
 __device__ __forceinline__ uint32_t lanemask_lt() { return (1u << (threadIdx.x & 31)) - 1u; }
 

@@ -85,9 +85,13 @@ struct RefNode {  // scene.cuh:82-100
 };
 static_assert(sizeof(RefNode) == 32, "reference node layout");
 
+struct PackedHalf {  // one child: box + reference, 32 bytes = one LDG.256
+    float box[6];
+    uint32_t ref;
+    uint32_t pad;
+};
 struct PackedRecord {
-    float f[12];
-    uint32_t ref[4];
+    PackedHalf child[2];
 };
 static_assert(sizeof(PackedRecord) == 64, "packed record");
 
@@ -98,7 +102,7 @@ struct Packer {
 
     static void set_box(PackedRecord &r, int child, const float *lo, const float *hi)
     {
-        float *b = r.f + 6 * child;
+        float *b = r.child[child].box;
         b[0] = lo[0]; b[1] = lo[1]; b[2] = lo[2];
         b[3] = hi[0]; b[4] = hi[1]; b[5] = hi[2];
     }
@@ -106,7 +110,7 @@ struct Packer {
     {
         const float far_away[3] = {3e38f, 3e38f, 3e38f};
         set_box(r, child, far_away, far_away);
-        r.ref[child] = kEmptyRef;
+        r.child[child].ref = kEmptyRef;
     }
     // triangles [begin, end) under box lo/hi -> a leaf ref, or a chain of same-box records when there are > 15
     uint32_t range_ref(int begin, int end, const float *lo, const float *hi, int depth)
@@ -122,8 +126,8 @@ struct Packer {
         uint32_t b = range_ref(mid, end, lo, hi, depth + 1);
         set_box(out[idx], 0, lo, hi);
         set_box(out[idx], 1, lo, hi);
-        out[idx].ref[0] = a;
-        out[idx].ref[1] = b;
+        out[idx].child[0].ref = a;
+        out[idx].child[1].ref = b;
         return (uint32_t)idx;
     }
     uint32_t node_ref(int i, int depth)
@@ -138,8 +142,8 @@ struct Packer {
         PackedRecord &r = out[idx];
         set_box(r, 0, nodes[n.child1].lo, nodes[n.child1].hi);
         set_box(r, 1, nodes[n.child2].lo, nodes[n.child2].hi);
-        r.ref[0] = a;
-        r.ref[1] = b;
+        r.child[0].ref = a;
+        r.child[1].ref = b;
         if (a == kEmptyRef) set_empty(r, 0);
         if (b == kEmptyRef) set_empty(r, 1);
         return (uint32_t)idx;
@@ -156,7 +160,7 @@ struct Packer {
             max_depth = 1;
             uint32_t a = node_count > 0 ? range_ref(nodes[0].child2, nodes[0].child1, nodes[0].lo, nodes[0].hi, 1) : kEmptyRef;
             if (a == kEmptyRef) set_empty(out[0], 0);
-            else { set_box(out[0], 0, nodes[0].lo, nodes[0].hi); out[0].ref[0] = a; }
+            else { set_box(out[0], 0, nodes[0].lo, nodes[0].hi); out[0].child[0].ref = a; }
             set_empty(out[0], 1);
         }
     }

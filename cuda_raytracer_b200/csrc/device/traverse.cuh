@@ -101,12 +101,11 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
         if (!(cur & kLeafBit)) {
             const float4 *n = nodes + 4 * (size_t)cur;
             const Float8 na = ldg256(n), nb = ldg256(n + 2);
-            const float4 q0 = na.lo, q1 = na.hi, q2 = nb.lo;
-            const uint2 q3 = make_uint2(__float_as_uint(nb.hi.x), __float_as_uint(nb.hi.y));
+            const uint2 q3 = make_uint2(__float_as_uint(na.hi.z), __float_as_uint(nb.hi.z));
             if (STATS) ctr.internal_visits++;
             float d0, d1;
-            bool h0 = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv, sg, closest, d0);
-            bool h1 = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv, sg, closest, d1);
+            bool h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, o, inv, sg, closest, d0);
+            bool h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, o, inv, sg, closest, d1);
             if (h0 && h1) {
                 bool zero_near = d0 < d1;
                 uint32_t far_ref = zero_near ? q3.y : q3.x;
@@ -191,6 +190,7 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
     const uint32_t batch = max(4u, min(tune.batch, (n + warps - 1) / warps));
     const uint32_t refill_below = tune.refill_below;
     const uint32_t node_min = tune.node_min;
+    const uint32_t half_first = (lane & 1u) * 2u;  // in float4 units: which half of a record this lane reads first
     uint32_t pool_next = 0, pool_end = 0;  // warp-uniform: unclaimed part of the current batch
     bool exhausted = false;                // warp-uniform: the global cursor ran past n
     bool busy = false;
@@ -243,13 +243,15 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
             // descend through internal records until this lane holds a leaf (or runs dry)
             while (!(cur & kLeafBit)) {
                 const float4 *nd = nodes + 4 * (size_t)cur;
-                const Float8 na = ldg256(nd), nb = ldg256(nd + 2);
-                const float4 q0 = na.lo, q1 = na.hi, q2 = nb.lo;
-                const uint2 q3 = make_uint2(__float_as_uint(nb.hi.x), __float_as_uint(nb.hi.y));
+                // The two halves of a record are symmetric (box + ref of one child each), so odd lanes fetch them in
+                // the opposite order: one LDG.256 then covers all four 32-byte sector positions of the L1 lines
+                // instead of two, which halves its data-pipe wavefronts (the kernel's busiest unit, profiles/r1c).
+                const Float8 na = ldg256(nd + half_first), nb = ldg256(nd + (half_first ^ 2u));
+                const uint2 q3 = make_uint2(__float_as_uint(na.hi.z), __float_as_uint(nb.hi.z));
                 if (STATS) ctr.internal_visits++;
                 float d0, d1;
-                const bool h0 = slab(q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, o, inv, sg, closest, d0);
-                const bool h1 = slab(q1.z, q1.w, q2.x, q2.y, q2.z, q2.w, o, inv, sg, closest, d1);
+                const bool h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, o, inv, sg, closest, d0);
+                const bool h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, o, inv, sg, closest, d1);
                 if (h0 && h1) {
                     const bool zero_near = d0 < d1;
                     stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
