@@ -286,6 +286,29 @@ __global__ void __launch_bounds__(kBlock, kBlocksPerSM) process_kernel(const Dev
     }
 }
 
+// ---- scene upload: layout conversion on the device (Scene::copy_from_cpu_async, scene.cu:243-265) ------------------
+// The caller's arrays arrive in the reference's layouts; these two kernels expand them into the device layouts of
+// device_scene.cuh, so the host never touches the 30 MB of triangles / texels.
+__global__ void pack_triangles_kernel(const float *__restrict__ tri12, const uint16_t *__restrict__ tri_materials, float4 *__restrict__ out,
+                                      uint32_t n)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *t = tri12 + 12 * (size_t)i;  // p1, e1, e2, n
+    float4 *o = out + 4 * (size_t)i;
+    o[0] = make_float4(t[0], t[1], t[2], t[3]);
+    o[1] = make_float4(t[4], t[5], t[6], t[7]);
+    o[2] = make_float4(t[8], t[9], t[10], t[11]);
+    o[3] = make_float4(__uint_as_float((uint32_t)tri_materials[i]), 0.0f, 0.0f, 0.0f);
+}
+
+__global__ void pack_env_kernel(const float *__restrict__ rgb, float4 *__restrict__ out, size_t texels)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= texels) return;
+    out[i] = make_float4(rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2], 0.0f);
+}
+
 // ---- post-process: bloom (raytracing.cu:21-74,360-392) and tone map (:286-303) ------------------------------------
 // The reference runs four kernels (high-pass, H blur, V blur, add); here the high-pass is folded into the H blur's
 // taps and the add into the V blur. Tap order and arithmetic are the reference's, so results are bit-identical to the

@@ -31,6 +31,9 @@ struct rt_ctx {
     bool has_scene = false;
     DeviceScene ds{};
     void *d_nodes = nullptr, *d_tris = nullptr, *d_materials = nullptr, *d_spheres = nullptr, *d_env = nullptr, *d_matidx = nullptr;
+    size_t cap_nodes = 0, cap_tris = 0, cap_materials = 0, cap_spheres = 0, cap_env = 0, cap_matidx = 0, cap_raw = 0, cap_stage = 0;
+    void *d_raw = nullptr;    // upload scratch: the caller's raw triangles + texels before the device-side repack
+    void *h_stage = nullptr;  // pinned staging for the packed BVH records
     int ray_count = 0, bounces = 0;
     float exposure = 0;
     int packed_nodes = 0, packed_depth = 0;
@@ -166,10 +169,22 @@ struct Packer {
     }
 };
 
-int upload(rt_ctx *ctx, void **dst, const void *src, size_t bytes)
+// Grow-only device buffer: re-uploading a scene of the same size allocates nothing.
+int reserve(rt_ctx *ctx, void **dst, size_t *cap, size_t bytes)
 {
+    bytes = std::max<size_t>(bytes, 16);
+    if (*dst && *cap >= bytes) return RT_OK;
     release(*dst);
-    RT_CUDA(ctx, cudaMalloc(dst, std::max<size_t>(bytes, 16)));
+    *cap = 0;
+    RT_CUDA(ctx, cudaMalloc(dst, bytes));
+    *cap = bytes;
+    return RT_OK;
+}
+
+int upload(rt_ctx *ctx, void **dst, size_t *cap, const void *src, size_t bytes)
+{
+    int rc = reserve(ctx, dst, cap, bytes);
+    if (rc != RT_OK) return rc;
     if (bytes) RT_CUDA(ctx, cudaMemcpyAsync(*dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
     return RT_OK;
 }
@@ -241,7 +256,8 @@ extern "C" void rt_destroy(rt_ctx *ctx)
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     release(ctx->d_nodes); release(ctx->d_tris); release(ctx->d_materials); release(ctx->d_spheres); release(ctx->d_env);
-    release(ctx->d_matidx); release(ctx->d_fb); release(ctx->d_fb_tmp); release(ctx->d_fb_tmp2); release(ctx->d_rgb8);
+    release(ctx->d_matidx); release(ctx->d_raw); if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    release(ctx->d_fb); release(ctx->d_fb_tmp); release(ctx->d_fb_tmp2); release(ctx->d_rgb8);
     for (int i = 0; i < 2; i++) {
         release(ctx->queue[i].qa); release(ctx->queue[i].qb); release(ctx->queue[i].qc);
         release(ctx->d_keys[i]); release(ctx->d_vals[i]);
@@ -283,29 +299,38 @@ extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *s)
     ctx->packed_nodes = (int)packer.out.size();
     ctx->packed_depth = packer.max_depth;
 
-    // triangles: 64-byte records {p1, e1, e2.xy | e2.z, n, material index, pad} (device_scene.cuh)
-    std::vector<float> tri4((size_t)s->triangle_count * 16, 0.0f);
-    for (int i = 0; i < s->triangle_count; i++) {
-        const float *t = s->triangles + 12 * (size_t)i;  // p1, e1, e2, n
-        float *o = &tri4[16 * (size_t)i];
-        for (int k = 0; k < 12; k++) o[k] = t[k];
-        const uint32_t mat = s->material_indices[s->sphere_count + i];
-        std::memcpy(&o[12], &mat, sizeof(mat));
+    const int prims = s->sphere_count + s->triangle_count;
+    const size_t texels = (size_t)s->env_width * s->env_height;
+    const size_t node_bytes = packer.out.size() * sizeof(PackedRecord);
+    const size_t raw_tri = (size_t)s->triangle_count * 48, raw_env = texels * 12;
+    // the previous upload's staging must have drained before it is overwritten
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->cap_stage < node_bytes) {
+        if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+        ctx->h_stage = nullptr;
+        ctx->cap_stage = 0;
+        RT_CUDA(ctx, cudaMallocHost(&ctx->h_stage, std::max<size_t>(node_bytes, 64)));
+        ctx->cap_stage = std::max<size_t>(node_bytes, 64);
     }
-    size_t texels = (size_t)s->env_width * s->env_height;
-    std::vector<float> env4(texels * 4);
-    for (size_t i = 0; i < texels; i++) {
-        env4[4 * i] = s->environment_map[3 * i]; env4[4 * i + 1] = s->environment_map[3 * i + 1];
-        env4[4 * i + 2] = s->environment_map[3 * i + 2]; env4[4 * i + 3] = 0.0f;
+    std::memcpy(ctx->h_stage, packer.out.data(), node_bytes);
+    if ((rc = upload(ctx, &ctx->d_nodes, &ctx->cap_nodes, ctx->h_stage, node_bytes)) != RT_OK) return rc;
+    if ((rc = upload(ctx, &ctx->d_materials, &ctx->cap_materials, s->materials, (size_t)s->material_count * 48)) != RT_OK) return rc;
+    if ((rc = upload(ctx, &ctx->d_spheres, &ctx->cap_spheres, s->spheres, (size_t)s->sphere_count * 16)) != RT_OK) return rc;
+    if ((rc = upload(ctx, &ctx->d_matidx, &ctx->cap_matidx, s->material_indices, (size_t)prims * sizeof(uint16_t))) != RT_OK) return rc;
+    // triangles and texels: raw copy, then repack on the device (pack_triangles_kernel / pack_env_kernel)
+    if ((rc = reserve(ctx, &ctx->d_raw, &ctx->cap_raw, std::max(raw_tri, raw_env))) != RT_OK) return rc;
+    if ((rc = reserve(ctx, &ctx->d_tris, &ctx->cap_tris, (size_t)s->triangle_count * 64)) != RT_OK) return rc;
+    if ((rc = reserve(ctx, &ctx->d_env, &ctx->cap_env, texels * 16)) != RT_OK) return rc;
+    if (s->triangle_count > 0) {
+        RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_raw, s->triangles, raw_tri, cudaMemcpyHostToDevice, ctx->stream));
+        pack_triangles_kernel<<<(s->triangle_count + 255) / 256, 256, 0, ctx->stream>>>(
+            (const float *)ctx->d_raw, (const uint16_t *)ctx->d_matidx + s->sphere_count, (float4 *)ctx->d_tris, (uint32_t)s->triangle_count);
     }
-    int prims = s->sphere_count + s->triangle_count;
-    if ((rc = upload(ctx, &ctx->d_nodes, packer.out.data(), packer.out.size() * sizeof(PackedRecord))) != RT_OK) return rc;
-    if ((rc = upload(ctx, &ctx->d_tris, tri4.data(), tri4.size() * sizeof(float))) != RT_OK) return rc;
-    if ((rc = upload(ctx, &ctx->d_materials, s->materials, (size_t)s->material_count * 48)) != RT_OK) return rc;
-    if ((rc = upload(ctx, &ctx->d_spheres, s->spheres, (size_t)s->sphere_count * 16)) != RT_OK) return rc;
-    if ((rc = upload(ctx, &ctx->d_env, env4.data(), env4.size() * sizeof(float))) != RT_OK) return rc;
-    if ((rc = upload(ctx, &ctx->d_matidx, s->material_indices, (size_t)prims * sizeof(uint16_t))) != RT_OK) return rc;
-    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // staging vectors die at return
+    RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_raw, s->environment_map, raw_env, cudaMemcpyHostToDevice, ctx->stream));
+    pack_env_kernel<<<(unsigned)((texels + 255) / 256), 256, 0, ctx->stream>>>((const float *)ctx->d_raw, (float4 *)ctx->d_env, texels);
+    RT_CUDA(ctx, cudaGetLastError());
+    // no synchronisation: copies from the caller's pageable arrays are staged by the runtime before the call returns,
+    // and everything else is ordered on the context's stream ahead of the first render kernel
 
     DeviceScene &d = ctx->ds;
     d.nodes = static_cast<const float4 *>(ctx->d_nodes);

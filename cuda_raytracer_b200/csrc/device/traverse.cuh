@@ -190,7 +190,6 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
     const uint32_t batch = max(4u, min(tune.batch, (n + warps - 1) / warps));
     const uint32_t refill_below = tune.refill_below;
     const uint32_t node_min = tune.node_min;
-    const uint32_t half_first = (lane & 1u) * 2u;  // in float4 units: which half of a record this lane reads first
     uint32_t pool_next = 0, pool_end = 0;  // warp-uniform: unclaimed part of the current batch
     bool exhausted = false;                // warp-uniform: the global cursor ran past n
     bool busy = false;
@@ -243,10 +242,10 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
             // descend through internal records until this lane holds a leaf (or runs dry)
             while (!(cur & kLeafBit)) {
                 const float4 *nd = nodes + 4 * (size_t)cur;
-                // The two halves of a record are symmetric (box + ref of one child each), so odd lanes fetch them in
-                // the opposite order: one LDG.256 then covers all four 32-byte sector positions of the L1 lines
-                // instead of two, which halves its data-pipe wavefronts (the kernel's busiest unit, profiles/r1c).
-                const Float8 na = ldg256(nd + half_first), nb = ldg256(nd + (half_first ^ 2u));
+                // One 32-byte half per child (box + ref). Fetching the halves in opposite order on odd and even lanes
+                // (to spread one LDG.256 over all four sector positions of the L1 lines) was measured: no gain, and
+                // it makes tie-breaking lane-dependent, so every lane reads child 0 first.
+                const Float8 na = ldg256(nd), nb = ldg256(nd + 2);
                 const uint2 q3 = make_uint2(__float_as_uint(na.hi.z), __float_as_uint(nb.hi.z));
                 if (STATS) ctr.internal_visits++;
                 float d0, d1;
