@@ -109,7 +109,8 @@ __global__ void __launch_bounds__(kBlock, SMEM ? kBlocksPerSM : kBlocksPerSMLoca
         SmemStack<kBlock> stack(stack_smem, a.stack_depth);
         trace_persistent<STATS>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below, a.trace_node_min});
     } else {
-        LocalStack stack;
+        __shared__ uint2 stack_top[kStackTop > 0 ? kStackTop : 1][kBlock];
+        HybridStack<kBlock> stack(&stack_top[0][0]);
         trace_persistent<STATS>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below, a.trace_node_min});
     }
     flush_trace_counters<STATS>(ctr, a.totals);
@@ -237,7 +238,8 @@ __global__ void __launch_bounds__(kBlock, SMEM ? kBlocksPerSM : kBlocksPerSMLoca
         SmemStack<kBlock> stack(stack_smem, stack_depth);
         trace_persistent<STATS>(sc, n, cursor, stack, io, ctr, tune);
     } else {
-        LocalStack stack;
+        __shared__ uint2 stack_top[kStackTop > 0 ? kStackTop : 1][kBlock];
+        HybridStack<kBlock> stack(&stack_top[0][0]);
         trace_persistent<STATS>(sc, n, cursor, stack, io, ctr, tune);
     }
     flush_trace_counters<STATS>(ctr, totals);

@@ -20,6 +20,10 @@ __device__ __forceinline__ float3 cross(float3 a, float3 b)
 __device__ __forceinline__ float length2(float3 a) { return a.x * a.x + a.y * a.y + a.z * a.z; }
 // (1/|v|) * v with IEEE sqrt and division, as math.cuh:110-113 on the host
 __device__ __forceinline__ float3 unit(float3 a) { return (1.0f / sqrtf(length2(a))) * a; }
+// Shading-only variants on the SFU (MUFU.RSQ / MUFU.SIN / MUFU.COS): ~2 ulp and |err| < 5e-7 for phi in [0, 2 pi],
+// far inside the 2e-4 shading tolerance of the parity tests; the reference's own GPU build uses the same fast-math
+// instructions (--use_fast_math, build.sh:2). Ray generation keeps the IEEE forms (it is checked bit for bit).
+__device__ __forceinline__ float3 unit_fast(float3 a) { return rsqrtf(length2(a)) * a; }
 __device__ __forceinline__ bool is_zero(float3 a) { return a.x == 0.0f && a.y == 0.0f && a.z == 0.0f; }
 
 // Same sums with contraction forbidden: used where the result must equal the host oracle bit for bit
@@ -78,7 +82,7 @@ __device__ __forceinline__ float3 rnd_on_sphere(Pcg &r)  // random.cuh:63-75
     float r2 = rnd02(r);
     float x = sqrtf(r2 * (2.0f - r2));
     float s, c;
-    sincosf(phi, &s, &c);
+    __sincosf(phi, &s, &c);
     return f3(c * x, s * x, 1.0f - r2);
 }
 

@@ -92,7 +92,7 @@ __device__ __forceinline__ void shade_hit(const DeviceScene &sc, float3 &o, floa
 
     bool front = dot(n, d) < 0.0f;
     if (!front) n = -n;
-    float3 nr = unit(n + roughness * rnd_on_sphere(rng));
+    float3 nr = unit_fast(n + roughness * rnd_on_sphere(rng));
     float cos_theta = dot(nr, d);
 
     if (ior == 0.0f) {
@@ -101,7 +101,7 @@ __device__ __forceinline__ void shade_hit(const DeviceScene &sc, float3 &o, floa
             d = d - (2.0f * cos_theta) * nr;  // not renormalised (Q11)
         } else {
             T = T * diffuse;
-            d = unit(n + rnd_on_sphere(rng));
+            d = unit_fast(n + rnd_on_sphere(rng));
         }
     } else {
         float inv_ior = 1.0f / ior;
@@ -118,7 +118,7 @@ __device__ __forceinline__ void shade_hit(const DeviceScene &sc, float3 &o, floa
             T = T * diffuse;
             float3 perp = ior * (d - cos_theta * nr);
             float3 par = (-sqrtf(1.0f - length2(perp))) * nr;
-            d = unit(par + perp);
+            d = unit_fast(par + perp);
         }
     }
 }

@@ -164,12 +164,33 @@ struct SmemStack {
     __device__ __forceinline__ void push(int sp, uint32_t r, float d) { ref[sp * BLOCK] = r; dist[sp * BLOCK] = d; }
     __device__ __forceinline__ void get(int sp, uint32_t &r, float &d) const { r = ref[sp * BLOCK]; d = dist[sp * BLOCK]; }
 };
-struct LocalStack {  // thread-local array: the hardware interleaves local memory per lane, lines live in L1
-    uint2 e[kStackDepth];  // {ref, entry distance bits}: one 64-bit STL / LDL per push / pop
-    __device__ __forceinline__ void push(int sp, uint32_t r, float d) { e[sp] = make_uint2(r, __float_as_uint(d)); }
+#ifndef RT_UNIFIED_POP
+#define RT_UNIFIED_POP 0
+#endif
+#ifndef RT_STACK_TOP
+#define RT_STACK_TOP 8
+#endif
+constexpr int kStackTop = RT_STACK_TOP;  // entries per thread kept in shared memory; deeper ones go to local memory
+
+// Default stack: the first kStackTop entries of every thread live in shared memory ([entry][thread]: the 32 lanes of
+// a warp hit 32 banks whatever their individual depths are, one data-pipe wavefront per access), the rest in a
+// thread-local array. A purely local stack scatters: lanes at different depths touch different 128-byte lines, and
+// ncu showed those accesses as 28 % of the L1 data-pipe load of the tracer (profiles/r1c). 8 entries x 128 threads x
+// 8 B = 8 KB per CTA leaves the L1 to the BVH, unlike a full-depth shared stack (SmemStack).
+template <int BLOCK>
+struct HybridStack {
+    uint2 *top;  // &smem[0][threadIdx.x]
+    uint2 deep[kStackDepth - kStackTop > 0 ? kStackDepth - kStackTop : 1];
+    __device__ __forceinline__ explicit HybridStack(uint2 *smem) : top(smem + threadIdx.x) {}
+    __device__ __forceinline__ void push(int sp, uint32_t r, float d)
+    {
+        const uint2 v = make_uint2(r, __float_as_uint(d));
+        if (sp < kStackTop) top[sp * BLOCK] = v;
+        else deep[sp - kStackTop] = v;
+    }
     __device__ __forceinline__ void get(int sp, uint32_t &r, float &d) const
     {
-        const uint2 v = e[sp];
+        const uint2 v = sp < kStackTop ? top[sp * BLOCK] : deep[sp - kStackTop];
         r = v.x;
         d = __uint_as_float(v.y);
     }
@@ -239,6 +260,45 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
 
         // ---- walk: lanes leave individually, the warp reconverges at the __syncwarp below ----
         while (busy) {
+#if RT_UNIFIED_POP
+            // Variant with ONE pop site at the head of the descent loop (lanes coming back from a leaf and lanes whose
+            // two children were both missed pop together). kEmptyRef doubles as "pop next": it is a leaf of zero triangles.
+            for (;;) {
+                if (cur == kEmptyRef) {
+                    float entry;  // pop, culling entries that can no longer beat the current hit (scene.cu:150-153)
+                    do {
+                        if (sp == 0) { cur = kDoneRef; break; }
+                        sp--;
+                        stack.get(sp, cur, entry);
+                    } while (entry >= closest);
+                }
+                if (cur & kLeafBit) break;
+                const float4 *nd = nodes + 4 * (size_t)cur;
+                const Float8 na = ldg256(nd), nb = ldg256(nd + 2);
+                const uint2 q3 = make_uint2(__float_as_uint(na.hi.z), __float_as_uint(nb.hi.z));
+                if (STATS) ctr.internal_visits++;
+                float d0, d1;
+                const bool h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, o, inv, sg, closest, d0);
+                const bool h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, o, inv, sg, closest, d1);
+                if (h0 && h1) {
+                    const bool zero_near = d0 < d1;
+                    stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
+                    sp++;
+                    cur = zero_near ? q3.x : q3.y;
+                } else {
+                    cur = h0 ? q3.x : h1 ? q3.y : kEmptyRef;
+                }
+                if (__popc(__activemask()) < node_min) break;
+            }
+            if ((cur & kLeafBit) && cur != kDoneRef) {
+                const uint32_t first = cur & kLeafStartMask;
+                const uint32_t count = (cur >> kLeafCountShift) & 15u;
+                if (STATS) ctr.triangle_tests += count;
+                for (uint32_t k = 0; k < count; k++) intersect_triangle(sc.tris, first + k, sc.sphere_count, o, d, closest, prim);
+                cur = kEmptyRef;
+                if (sp == 0) cur = kDoneRef;
+            }
+#else
             // descend through internal records until this lane holds a leaf (or runs dry)
             while (!(cur & kLeafBit)) {
                 const float4 *nd = nodes + 4 * (size_t)cur;
@@ -283,6 +343,7 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
                     stack.get(sp, cur, entry);
                 } while (entry >= closest);
             }
+#endif
             if (cur == kDoneRef) {
                 io.store(slot, closest, prim);
                 busy = false;

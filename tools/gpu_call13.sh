@@ -1,0 +1,13 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" >> gpurun_out/pytest_gpu.log
+P=gpurun_out/probe13.log
+echo "== default (top 8)" >> $P
+timeout 600 python tools/perf_probe.py lamp 3840 2160 80 10 group4 noref >> $P 2>&1
+timeout 600 python tools/perf_probe.py lamp 1000 1000 320 10 group16 noref >> $P 2>&1
+for n in 0 4 12 16; do
+  echo "== RT_STACK_TOP=$n" >> $P
+  RT_LIBRTCORE=$PWD/cuda_raytracer_b200/librtcore_top$n.so timeout 600 python tools/perf_probe.py lamp 3840 2160 80 10 group4 noref >> $P 2>&1
+  RT_LIBRTCORE=$PWD/cuda_raytracer_b200/librtcore_top$n.so timeout 600 python tools/perf_probe.py lamp 1000 1000 320 10 group16 noref >> $P 2>&1
+done
+timeout 600 python bench.py --no-ref-gpu --no-cpu-baseline > gpurun_out/bench.json 2> gpurun_out/bench.err
