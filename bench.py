@@ -63,7 +63,7 @@ class ClockSampler:
               "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, gpu_index):
-        self.gpu_index, self.rows, self.proc = str(gpu_index), [], None
+        self.gpu_index, self.rows, self.proc, self.first = str(gpu_index), [], None, 0
 
     def start(self):
         try:
@@ -79,9 +79,14 @@ class ClockSampler:
             if len(f) >= 8 and f[0] == self.gpu_index:
                 self.rows.append(f)
 
+    def mark(self):
+        """Start of the timed region: rows sampled before this point (warm-up) are not reported."""
+        self.first = max(0, len(self.rows) - 1)
+
     def stop(self):
         if self.proc:
             self.proc.terminate()
+        self.rows = self.rows[self.first:]
         sm = sorted(float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit())
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for k, n in enumerate(names) if any(r[4 + k].lower().startswith("active") for r in self.rows)]
@@ -313,11 +318,12 @@ def main():
     # the dominant kernel (trace_rays_kernel) alone: ray read 32 B + hit record 8 B + BVH records
     trace_bytes_per_unit = 40.0 + 64.0 * n_int + 48.0 * n_tri
 
+    sampler = ClockSampler(visible_gpu_index(local_rank))
+    sampler.start()  # nvidia-smi needs ~0.5 s to deliver its first row: start it ahead of the warm-up
     for _ in range(args.warmup):
         frame()
-    sampler = ClockSampler(visible_gpu_index(local_rank))
     barrier()
-    sampler.start()
+    sampler.mark()
     wall0 = time.perf_counter()
     per_step = [frame(timing=True) for _ in range(args.steps)]
     barrier()

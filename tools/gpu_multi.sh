@@ -1,10 +1,9 @@
 #!/bin/bash
-# usage: gpu_multi.sh N  — scaling runs of bench.py at 1..N GPUs of one box (launched exactly as the driver does)
-N=${1:-2}
+# usage: gpu_multi.sh "1 2 4 8" — scaling runs of bench.py on one box (launched exactly as the driver does)
+LIST=${1:-"1 2"}
 mkdir -p gpurun_out
 nvidia-smi -L > gpurun_out/smi_multi.txt
-for n in 1 2 4 8; do
-  [ $n -gt $N ] && break
+for n in $LIST; do
   if [ $n -eq 1 ]; then
     timeout 900 python bench.py --gpus 1 --no-cpu-baseline --no-ref-gpu > gpurun_out/scale_$n.json 2> gpurun_out/scale_$n.err
   else
