@@ -164,9 +164,6 @@ struct SmemStack {
     __device__ __forceinline__ void push(int sp, uint32_t r, float d) { ref[sp * BLOCK] = r; dist[sp * BLOCK] = d; }
     __device__ __forceinline__ void get(int sp, uint32_t &r, float &d) const { r = ref[sp * BLOCK]; d = dist[sp * BLOCK]; }
 };
-#ifndef RT_UNIFIED_POP
-#define RT_UNIFIED_POP 0
-#endif
 #ifndef RT_STACK_TOP
 #define RT_STACK_TOP 8
 #endif
@@ -260,45 +257,6 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
 
         // ---- walk: lanes leave individually, the warp reconverges at the __syncwarp below ----
         while (busy) {
-#if RT_UNIFIED_POP
-            // Variant with ONE pop site at the head of the descent loop (lanes coming back from a leaf and lanes whose
-            // two children were both missed pop together). kEmptyRef doubles as "pop next": it is a leaf of zero triangles.
-            for (;;) {
-                if (cur == kEmptyRef) {
-                    float entry;  // pop, culling entries that can no longer beat the current hit (scene.cu:150-153)
-                    do {
-                        if (sp == 0) { cur = kDoneRef; break; }
-                        sp--;
-                        stack.get(sp, cur, entry);
-                    } while (entry >= closest);
-                }
-                if (cur & kLeafBit) break;
-                const float4 *nd = nodes + 4 * (size_t)cur;
-                const Float8 na = ldg256(nd), nb = ldg256(nd + 2);
-                const uint2 q3 = make_uint2(__float_as_uint(na.hi.z), __float_as_uint(nb.hi.z));
-                if (STATS) ctr.internal_visits++;
-                float d0, d1;
-                const bool h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, o, inv, sg, closest, d0);
-                const bool h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, o, inv, sg, closest, d1);
-                if (h0 && h1) {
-                    const bool zero_near = d0 < d1;
-                    stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
-                    sp++;
-                    cur = zero_near ? q3.x : q3.y;
-                } else {
-                    cur = h0 ? q3.x : h1 ? q3.y : kEmptyRef;
-                }
-                if (__popc(__activemask()) < node_min) break;
-            }
-            if ((cur & kLeafBit) && cur != kDoneRef) {
-                const uint32_t first = cur & kLeafStartMask;
-                const uint32_t count = (cur >> kLeafCountShift) & 15u;
-                if (STATS) ctr.triangle_tests += count;
-                for (uint32_t k = 0; k < count; k++) intersect_triangle(sc.tris, first + k, sc.sphere_count, o, d, closest, prim);
-                cur = kEmptyRef;
-                if (sp == 0) cur = kDoneRef;
-            }
-#else
             // descend through internal records until this lane holds a leaf (or runs dry)
             while (!(cur & kLeafBit)) {
                 const float4 *nd = nodes + 4 * (size_t)cur;
@@ -343,7 +301,6 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
                     stack.get(sp, cur, entry);
                 } while (entry >= closest);
             }
-#endif
             if (cur == kDoneRef) {
                 io.store(slot, closest, prim);
                 busy = false;
