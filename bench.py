@@ -403,6 +403,13 @@ def main():
         "breakdown_ms_per_step": {"trace_kernels": tr_ms / args.steps, "shade_kernels": sh_ms / args.steps, "reorder": so_ms / args.steps, "nccl_reduce": red_s / args.steps * 1e3,
                                   "wall": wall / args.steps * 1e3},
     }
+    if world == 1:  # the same tree built on the device (csrc/device/bvh_build.cuh) vs the host builder
+        dev_scene = rt.load_scene(scene_name + ".scene", use_bvh="device", cwd=SCENES).set_image(w, h, spp, bounces)
+        r.upload(dev_scene)
+        r.upload(dev_scene)  # second upload: buffers exist, steady state
+        line["bvh_build_ms"] = {"host_binned_sah": scene.bvh_build_ms, "device_binned_sah": r.bvh_device_ms,
+                                "triangles": int(a.triangle_count), "nodes": int(a.bvh_node_count)}
+        r.upload(scene)
     if world == 1 and not args.no_cpu_baseline and os.path.exists(REF_BIN):
         ratio, threads = live_per_primary(scene_name, w, h, bounces)
         s_spp = size_cpu_sample(scene_name, w, h, bounces, 12.0)

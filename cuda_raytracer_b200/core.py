@@ -43,6 +43,7 @@ class SceneDesc(C.Structure):
         ("scaled_right", C.c_float * 3), ("scaled_up", C.c_float * 3),
         ("inv_width", C.c_float), ("inv_height", C.c_float),
         ("min_coord", C.c_float * 3), ("inv_dimensions", C.c_float * 3),
+        ("triangles_form", C.c_int32),
     ]
 
 
@@ -72,7 +73,7 @@ EXPORTS = [
     # rt_core.h
     "rt_api_version", "rt_device_count", "rt_create", "rt_destroy", "rt_last_error", "rt_scene_upload", "rt_scene_set_image",
     "rt_render", "rt_render_device", "rt_postprocess", "rt_framebuffer_upload", "rt_trace_closest", "rt_generate_rays",
-    "rt_process_rays", "rt_sort_pairs",
+    "rt_process_rays", "rt_sort_pairs", "rt_scene_download_bvh", "rt_scene_bvh_device_ms",
     # rt_scene.h
     "rt_scene_load", "rt_scene_free", "rt_scene_describe", "rt_scene_set_image_host", "rt_scene_camera_raw",
     "rt_scene_bvh_build_ms", "rt_write_png",
@@ -106,6 +107,9 @@ def lib():
     L.rt_generate_rays.argtypes = [vp, i32, i32, i32, i32, vp]
     L.rt_process_rays.argtypes = [vp, vp, vp, i32]
     L.rt_sort_pairs.argtypes = [vp, vp, vp, i32, i32]
+    L.rt_scene_download_bvh.argtypes = [vp, vp, i32, C.POINTER(i32), vp, i32]
+    L.rt_scene_bvh_device_ms.argtypes = [vp]
+    L.rt_scene_bvh_device_ms.restype = C.c_double
     L.rt_scene_load.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(vp)]
     L.rt_scene_free.argtypes = [vp]
     L.rt_scene_free.restype = None
@@ -136,12 +140,15 @@ class Scene:
     """A host scene (rt_host_scene): what the reference's ``load_scene`` fills into its ``Scene`` struct."""
 
     def __init__(self, path, use_bvh=True, verbose=False, cwd=None):
+        """use_bvh: True / False as the reference's flag; "device" (= 2) defers the BVH build to the GPU."""
+        if use_bvh == "device":
+            use_bvh = 2
         self._h = C.c_void_p()
         old = os.getcwd()
         if cwd:
             os.chdir(cwd)  # paths inside scene files are CWD-relative, as in the reference
         try:
-            _check(lib().rt_scene_load(os.fsencode(path), 1 if use_bvh else 0, 1 if verbose else 0, C.byref(self._h)))
+            _check(lib().rt_scene_load(os.fsencode(path), int(use_bvh), 1 if verbose else 0, C.byref(self._h)))
         finally:
             os.chdir(old)
 
@@ -187,6 +194,7 @@ class Scene:
             "bvh": _view(d.bvh_nodes, NODE_DTYPE, d.bvh_node_count).copy(),
             "env": _view(d.environment_map, np.float32, 3 * d.env_width * d.env_height).copy().reshape(-1, 3),
             "env_w": d.env_width, "env_h": d.env_height,
+            "triangles_form": d.triangles_form,
             "width": d.width, "height": d.height, "ray_count": d.ray_count, "bounces": d.bounces,
             "exposure": np.float32(d.exposure),
             "camera_position": np.array(d.camera_position[:], np.float32),
@@ -298,6 +306,19 @@ class Renderer:
         assert len(s) == len(d)
         _check(lib().rt_process_rays(self._ctx, d.ctypes.data, s.ctypes.data, len(d)), self._ctx)
         return d
+
+    def download_bvh(self, triangle_count):
+        """After uploading a scene loaded with use_bvh="device": (nodes[NODE_DTYPE], order int32[triangle_count])."""
+        n = C.c_int32()
+        _check(lib().rt_scene_download_bvh(self._ctx, None, 0, C.byref(n), None, 0), self._ctx)
+        nodes = np.zeros(n.value, NODE_DTYPE)
+        order = np.zeros(triangle_count, np.int32)
+        _check(lib().rt_scene_download_bvh(self._ctx, nodes.ctypes.data, n.value, C.byref(n), order.ctypes.data, triangle_count), self._ctx)
+        return nodes, order
+
+    @property
+    def bvh_device_ms(self):
+        return lib().rt_scene_bvh_device_ms(self._ctx)
 
     def sort_pairs(self, keys, values, bits=32):
         k = np.ascontiguousarray(keys, np.uint32).copy()

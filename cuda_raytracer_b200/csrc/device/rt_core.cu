@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "../../../include/rt_core.h"
+#include "bvh_build.cuh"
 #include "kernels.cuh"
 #include "radix_sort.cuh"
 
@@ -34,6 +35,11 @@ struct rt_ctx {
     size_t cap_nodes = 0, cap_tris = 0, cap_materials = 0, cap_spheres = 0, cap_env = 0, cap_matidx = 0, cap_raw = 0, cap_stage = 0;
     void *d_raw = nullptr;    // upload scratch: the caller's raw triangles + texels before the device-side repack
     void *h_stage = nullptr;  // pinned staging for the packed BVH records
+    void *d_build = nullptr;  // device BVH build scratch: nodes, order buffers, level lists, counters
+    size_t cap_build = 0;
+    int32_t *d_order = nullptr;  // device build: BVH position -> file-order triangle id (inside d_build)
+    std::vector<uint8_t> built_nodes;  // device build: the reference-layout nodes it produced (32 B each)
+    double bvh_device_ms = 0;
     int ray_count = 0, bounces = 0;
     float exposure = 0;
     int packed_nodes = 0, packed_depth = 0;
@@ -256,7 +262,7 @@ extern "C" void rt_destroy(rt_ctx *ctx)
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     release(ctx->d_nodes); release(ctx->d_tris); release(ctx->d_materials); release(ctx->d_spheres); release(ctx->d_env);
-    release(ctx->d_matidx); release(ctx->d_raw); if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    release(ctx->d_matidx); release(ctx->d_raw); release(ctx->d_build); if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     release(ctx->d_fb); release(ctx->d_fb_tmp); release(ctx->d_fb_tmp2); release(ctx->d_rgb8);
     for (int i = 0; i < 2; i++) {
         release(ctx->queue[i].qa); release(ctx->queue[i].qb); release(ctx->queue[i].qc);
@@ -271,6 +277,73 @@ extern "C" void rt_destroy(rt_ctx *ctx)
     delete ctx;
 }
 
+namespace {
+
+// Device BVH build (bvh_build.cuh): level-synchronous, one CTA per node; the host only reads the size of the next
+// level. Leaves the build-form triangles in ctx->d_raw, the BVH-order permutation in ctx->d_order and the
+// reference-layout nodes in ctx->built_nodes.
+int build_bvh_on_device(rt_ctx *ctx, const rt_scene_desc *s, int max_depth)
+{
+    const int n = s->triangle_count;
+    const size_t max_nodes = (size_t)2 * n + 2;
+    const size_t bytes = max_nodes * sizeof(BuildNode) + (size_t)3 * n * 4 + 2 * max_nodes * 4 + 64;
+    int rc = reserve(ctx, &ctx->d_build, &ctx->cap_build, bytes);
+    if (rc != RT_OK) return rc;
+    if ((rc = reserve(ctx, &ctx->d_raw, &ctx->cap_raw, std::max<size_t>((size_t)n * 48, (size_t)s->env_width * s->env_height * 12))) != RT_OK) return rc;
+    uint8_t *base = static_cast<uint8_t *>(ctx->d_build);
+    BuildNode *nodes = reinterpret_cast<BuildNode *>(base);
+    int32_t *order_a = reinterpret_cast<int32_t *>(base + max_nodes * sizeof(BuildNode));
+    int32_t *order_b = order_a + n, *order_final = order_b + n;
+    int32_t *level_a = order_final + n, *level_b = level_a + max_nodes;
+    int32_t *counters = level_b + max_nodes;
+    ctx->d_order = order_final;
+
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
+    RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_raw, s->triangles, (size_t)n * 48, cudaMemcpyHostToDevice, ctx->stream));
+    BuildNode root{};
+    for (int k = 0; k < 3; k++) { root.lo[k] = 1e30f; root.hi[k] = -1e30f; }
+    root.child2 = 0;
+    root.child1 = n;
+    const int32_t init[3] = {1, 0, 0};  // nodes allocated, next-level size, level_a[0] = root
+    RT_CUDA(ctx, cudaMemcpyAsync(nodes, &root, sizeof(root), cudaMemcpyHostToDevice, ctx->stream));
+    RT_CUDA(ctx, cudaMemcpyAsync(counters, init, 2 * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+    RT_CUDA(ctx, cudaMemsetAsync(level_a, 0, sizeof(int32_t), ctx->stream));
+    if (n > 0) iota_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(order_a, n);
+
+    int level_count = 1, node_count = 1;
+    for (int level = 0; level_count > 0 && level <= max_depth; level++) {
+        BuildArgs a{};
+        a.tris = static_cast<const BuildTri *>(ctx->d_raw);
+        a.nodes = nodes;
+        a.order_in = (level & 1) ? order_b : order_a;
+        a.order_out = (level & 1) ? order_a : order_b;
+        a.order_final = order_final;
+        a.level_nodes = (level & 1) ? level_b : level_a;
+        a.next_nodes = (level & 1) ? level_a : level_b;
+        a.counters = counters;
+        a.level = level;
+        a.max_depth = max_depth;
+        bvh_level_kernel<<<level_count, kBuildBlock, 0, ctx->stream>>>(a);
+        int32_t c[2];
+        RT_CUDA(ctx, cudaMemcpyAsync(c, counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
+        RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        node_count = c[0];
+        level_count = c[1];
+        RT_CUDA(ctx, cudaMemsetAsync(counters + 1, 0, sizeof(int32_t), ctx->stream));
+    }
+    RT_CUDA(ctx, cudaGetLastError());
+    ctx->built_nodes.resize((size_t)node_count * sizeof(BuildNode));
+    RT_CUDA(ctx, cudaMemcpyAsync(ctx->built_nodes.data(), nodes, ctx->built_nodes.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    float ms = 0;
+    RT_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_start, ctx->ev_stop));
+    ctx->bvh_device_ms = ms;
+    return RT_OK;
+}
+
+}  // namespace
+
 extern "C" int rt_scene_set_image(rt_ctx *ctx, const rt_scene_desc *s)
 {
     if (!ctx || !s) return fail(ctx, RT_ERR_INVALID, "rt_scene_set_image: null argument");
@@ -281,8 +354,9 @@ extern "C" int rt_scene_set_image(rt_ctx *ctx, const rt_scene_desc *s)
 extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *s)
 {
     if (!ctx || !s) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: null argument");
-    if (s->sphere_count < 0 || s->triangle_count < 0 || s->material_count <= 0 || s->bvh_node_count <= 0 || !s->bvh_nodes ||
-        !s->materials || !s->environment_map || s->env_width <= 0 || s->env_height <= 0 ||
+    const bool device_build = s->triangles_form == 1;
+    if (s->sphere_count < 0 || s->triangle_count < 0 || s->material_count <= 0 || (!device_build && (s->bvh_node_count <= 0 || !s->bvh_nodes)) ||
+        s->triangles_form < 0 || s->triangles_form > 1 || !s->materials || !s->environment_map || s->env_width <= 0 || s->env_height <= 0 ||
         (s->triangle_count > 0 && !s->triangles) || (s->sphere_count > 0 && !s->spheres) ||
         (s->triangle_count + s->sphere_count > 0 && !s->material_indices))
         return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: malformed scene descriptor");
@@ -292,9 +366,13 @@ extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *s)
     int rc = set_image_block(ctx, s);
     if (rc != RT_OK) return rc;
 
+    ctx->built_nodes.clear();
+    ctx->d_order = nullptr;
+    ctx->bvh_device_ms = 0;
+    if (device_build && (rc = build_bvh_on_device(ctx, s, 30)) != RT_OK) return rc;  // MAX_BVH_DEPTH, scene.cu:10
     Packer packer;
-    packer.nodes = static_cast<const RefNode *>(s->bvh_nodes);
-    packer.run(s->bvh_node_count);
+    packer.nodes = device_build ? reinterpret_cast<const RefNode *>(ctx->built_nodes.data()) : static_cast<const RefNode *>(s->bvh_nodes);
+    packer.run(device_build ? (int)(ctx->built_nodes.size() / sizeof(RefNode)) : s->bvh_node_count);
     if (packer.max_depth > kStackDepth) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: BVH deeper than the traversal stack (32)");
     ctx->packed_nodes = (int)packer.out.size();
     ctx->packed_depth = packer.max_depth;
@@ -321,7 +399,11 @@ extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *s)
     if ((rc = reserve(ctx, &ctx->d_raw, &ctx->cap_raw, std::max(raw_tri, raw_env))) != RT_OK) return rc;
     if ((rc = reserve(ctx, &ctx->d_tris, &ctx->cap_tris, (size_t)s->triangle_count * 64)) != RT_OK) return rc;
     if ((rc = reserve(ctx, &ctx->d_env, &ctx->cap_env, texels * 16)) != RT_OK) return rc;
-    if (s->triangle_count > 0) {
+    if (s->triangle_count > 0 && device_build) {  // build-form triangles are already in d_raw; order = the build's permutation
+        pack_built_triangles_kernel<<<(s->triangle_count + 255) / 256, 256, 0, ctx->stream>>>(
+            (const BuildTri *)ctx->d_raw, ctx->d_order, (const uint16_t *)ctx->d_matidx + s->sphere_count, (float4 *)ctx->d_tris,
+            (uint32_t)s->triangle_count);
+    } else if (s->triangle_count > 0) {
         RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_raw, s->triangles, raw_tri, cudaMemcpyHostToDevice, ctx->stream));
         pack_triangles_kernel<<<(s->triangle_count + 255) / 256, 256, 0, ctx->stream>>>(
             (const float *)ctx->d_raw, (const uint16_t *)ctx->d_matidx + s->sphere_count, (float4 *)ctx->d_tris, (uint32_t)s->triangle_count);
@@ -831,5 +913,28 @@ extern "C" int rt_sort_pairs(rt_ctx *ctx, uint32_t *keys, uint32_t *values, int3
     RT_CUDA(ctx, cudaMemcpyAsync(keys, sk, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     RT_CUDA(ctx, cudaMemcpyAsync(values, sv, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return RT_OK;
+}
+
+// ---- device BVH build: inspection hooks ---------------------------------------------------------------------------
+extern "C" double rt_scene_bvh_device_ms(const rt_ctx *ctx) { return ctx ? ctx->bvh_device_ms : 0.0; }
+
+extern "C" int rt_scene_download_bvh(rt_ctx *ctx, void *nodes32, int32_t node_capacity, int32_t *node_count, int32_t *order,
+                                     int32_t order_capacity)
+{
+    if (!ctx || !node_count) return fail(ctx, RT_ERR_INVALID, "rt_scene_download_bvh: null argument");
+    if (!ctx->has_scene || ctx->built_nodes.empty()) return fail(ctx, RT_ERR_INVALID, "rt_scene_download_bvh: the BVH was not built on the device");
+    const int n = (int)(ctx->built_nodes.size() / sizeof(BuildNode));
+    *node_count = n;
+    if (nodes32) {
+        if (node_capacity < n) return fail(ctx, RT_ERR_INVALID, "rt_scene_download_bvh: node buffer too small");
+        std::memcpy(nodes32, ctx->built_nodes.data(), ctx->built_nodes.size());
+    }
+    if (order) {
+        if (order_capacity < ctx->ds.tri_count) return fail(ctx, RT_ERR_INVALID, "rt_scene_download_bvh: order buffer too small");
+        RT_CUDA(ctx, cudaSetDevice(ctx->device));
+        RT_CUDA(ctx, cudaMemcpyAsync(order, ctx->d_order, (size_t)ctx->ds.tri_count * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
     return RT_OK;
 }

@@ -172,4 +172,20 @@ void HostScene::build_tree(int max_depth, bool verbose)
     }
 }
 
+// Deferred build (rt_scene_load with use_bvh = 2): only the root node and its box exist on the host (the scene bounds of
+// scene.cu:822-830 need it); the render core builds the tree on the device from the build-form triangles.
+void HostScene::defer_tree(bool verbose)
+{
+    nodes.clear();
+    nodes.emplace_back();
+    nodes[0].child2 = 0;
+    nodes[0].child1 = (int)triangles.size();
+    Box box;
+    for (const TriRecord &t : triangles) box.grow(t);
+    nodes[0].box = box;
+    triangles_form = 1;
+    bvh_ms = 0;
+    if (verbose) std::printf("Triangle count: %d\n", (int)triangles.size());
+}
+
 }  // namespace rt

@@ -84,9 +84,11 @@ struct HostScene {
     float inv_width = 0, inv_height = 0;
     F3 min_coord, inv_dimensions;
     double bvh_ms = 0;
+    int triangles_form = 0;  // 1 = build form, file order: the BVH is built by the render core on the device
 
     void precompute_camera();
     void build_tree(int max_depth, bool verbose);  // bvh_builder.cpp
+    void defer_tree(bool verbose);                 // bvh_builder.cpp: root node only, triangles stay in build form
     void compute_bounds();
 };
 
@@ -96,6 +98,6 @@ struct LoadError {
 };
 
 // Throws LoadError. scene_loader.cpp
-void load_scene_file(HostScene &scene, const char *path, bool use_bvh, bool verbose);
+void load_scene_file(HostScene &scene, const char *path, int use_bvh, bool verbose);  // 0 no_bvh, 1 host build, 2 deferred
 
 }  // namespace rt

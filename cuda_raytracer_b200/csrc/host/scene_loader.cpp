@@ -146,7 +146,7 @@ void HostScene::compute_bounds()  // scene.cu:822-830; note inv = 1/max, not 1/(
     inv_dimensions = {1 / top.x, 1 / top.y, 1 / top.z};
 }
 
-void load_scene_file(HostScene &scene, const char *path, bool use_bvh, bool verbose)
+void load_scene_file(HostScene &scene, const char *path, int use_bvh, bool verbose)
 {
     std::ifstream file(path);
     if (!file) fail(RT_ERR_IO, std::string("cannot open scene file '") + path + "'");
@@ -229,7 +229,8 @@ void load_scene_file(HostScene &scene, const char *path, bool use_bvh, bool verb
         scene.env_w = scene.env_h = 1;
     }
     scene.precompute_camera();
-    scene.build_tree(use_bvh ? 30 : 0, verbose);  // MAX_BVH_DEPTH, scene.cu:10,820
+    if (use_bvh == 2) scene.defer_tree(verbose);
+    else scene.build_tree(use_bvh ? 30 : 0, verbose);  // MAX_BVH_DEPTH, scene.cu:10,820
     scene.compute_bounds();
 }
 

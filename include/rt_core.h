@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RT_API_VERSION 3
+#define RT_API_VERSION 4
 
 typedef enum rt_status {
     RT_OK = 0,
@@ -62,6 +62,10 @@ typedef struct rt_scene_desc {
     float inv_width, inv_height;
     float min_coord[3];                /* scene bounds for the reorder key               scene.cu:822-830 */
     float inv_dimensions[3];
+    int32_t triangles_form;            /* 0 = as above (what the reference's load_scene leaves behind). 1 = BUILD form, file order:
+                                          {p1, p2, p3, centroid} per triangle (scene.cu:520-531), material_indices in the same
+                                          order, bvh_nodes ignored: the core builds the BVH on the device with the reference's
+                                          binned-SAH rules (generate_bvh / maybe_split, scene.cu:866-1036). */
 } rt_scene_desc;
 
 typedef struct rt_render_opts {
@@ -111,6 +115,11 @@ const char *rt_last_error(const rt_ctx *ctx);
 /* Replaces Scene::copy_from_cpu_async + the __constant__ symbol (scene.cu:243-265, raytracing.cu:19):
  * packs the BVH into 64-byte two-child records and the triangles into 3 x float4, uploads all. */
 int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *scene);
+/* After an upload with triangles_form == 1: the tree the device built, in the reference's 32-byte node layout (numbered
+ * breadth-first), and order[i] = file-order id of the triangle at BVH position i. Either output may be NULL. */
+int rt_scene_download_bvh(rt_ctx *ctx, void *nodes32, int32_t node_capacity, int32_t *node_count, int32_t *order, int32_t order_capacity);
+/* CUDA-event time of that build (H2D of the triangles, all levels, D2H of the nodes), 0 if the host built the tree. */
+double rt_scene_bvh_device_ms(const rt_ctx *ctx);
 /* Change the image block without re-uploading geometry (width/height/ray_count/bounces/exposure + camera basis). */
 int rt_scene_set_image(rt_ctx *ctx, const rt_scene_desc *scene);
 

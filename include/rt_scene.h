@@ -24,6 +24,8 @@ typedef struct rt_host_scene rt_host_scene;
 
 /* Paths inside the scene file are relative to the current working directory (reference behaviour).
  * use_bvh = 0 reproduces the `no_bvh` flag: one root leaf holding every triangle (scene.cu:820, Q12).
+ * use_bvh = 2 defers the build to the device: triangles stay in build form and file order, the descriptor carries
+ * triangles_form = 1 and a single root node (its box is still computed, the scene bounds need it).
  * verbose != 0 prints the reference's stdout lines (Loaded environment map..., Triangle count, BVH Took, Node count). */
 int rt_scene_load(const char *path, int use_bvh, int verbose, rt_host_scene **out);
 void rt_scene_free(rt_host_scene *scene);

@@ -50,6 +50,9 @@ def test_command_line_writes_the_reference_outputs(tmp_path):
     assert "Node count: 1\n" in out2
     diff = np.sqrt(np.mean((img.astype(np.float64) - img2.astype(np.float64)) ** 2))
     assert diff < 6.0  # same streams, same geometry: only bloom-threshold flips and float order differ
+    img4, out4 = _run(EXE, tmp_path, scene, "gpu_bvh")  # tree built on the device: same node count, same picture
+    assert "Node count: 81311" in out4 and "BVH Took" in out4
+    assert np.sqrt(np.mean((img.astype(np.float64) - img4.astype(np.float64)) ** 2)) < 6.0
     img3, out3 = _run(EXE, tmp_path, scene, "stats", "out=custom.png", png="custom.png")
     assert img3.shape == img.shape and '"mrays_per_s"' in out3 and not os.path.exists(tmp_path / "raytracing.png")
 
