@@ -72,12 +72,17 @@ __global__ void __launch_bounds__(256) sort_scan_kernel(SortArgs s)
 }
 
 // One digit pass. values_in == nullptr means "value = element index" (first pass of a fresh permutation).
+// The tile is ranked, re-ordered by digit in shared memory and only then written out, so that consecutive threads
+// store consecutive addresses of a digit's run (a direct scatter writes 32 different sectors per warp instruction).
 __global__ void __launch_bounds__(kSortBlock) sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ values_in,
                                                                    uint32_t *__restrict__ keys_out, uint32_t *__restrict__ values_out,
                                                                    SortArgs s, int pass)
 {
-    __shared__ uint32_t warp_hist[kSortWarps][256];
-    __shared__ uint32_t digit_base[256];
+    __shared__ uint32_t warp_hist[kSortWarps][256];  // per-warp digit counts -> exclusive offsets of the warp inside the tile's digit run
+    __shared__ uint32_t digit_base[256];             // global position of the tile's first key of each digit
+    __shared__ uint32_t digit_start[256];            // position of that key inside the digit-ordered tile
+    __shared__ uint32_t warp_total[kSortWarps];
+    __shared__ uint32_t stage_key[kSortTile], stage_val[kSortTile];
     __shared__ uint32_t tile_id_sh;
 
     const uint32_t n = *s.count_ptr;
@@ -90,7 +95,9 @@ __global__ void __launch_bounds__(kSortBlock) sort_scatter_kernel(const uint32_t
 
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t shift = 8u * pass;
-    const uint32_t warp_base = tile * kSortTile + warp * (kSortItems * 32u);
+    const uint32_t tile_base = tile * kSortTile;
+    const uint32_t warp_base = tile_base + warp * (kSortItems * 32u);
+    const uint32_t tile_n = min((uint32_t)kSortTile, n - tile_base);
     const uint32_t lt = (1u << lane) - 1u;
 
     uint32_t key[kSortItems], val[kSortItems];
@@ -99,8 +106,8 @@ __global__ void __launch_bounds__(kSortBlock) sort_scatter_kernel(const uint32_t
     for (int r = 0; r < kSortItems; r++) {
         uint32_t i = warp_base + r * 32u + lane;
         bool valid = i < n;
-        key[r] = valid ? keys_in[i] : 0xFFFFFFFFu;
-        val[r] = valid ? (values_in ? values_in[i] : i) : 0u;
+        key[r] = valid ? __ldcs(keys_in + i) : 0xFFFFFFFFu;
+        val[r] = valid ? (values_in ? __ldcs(values_in + i) : i) : 0u;
     }
     // stable ranking inside the warp's 512-key segment: rounds in memory order, lanes in order within a round
 #pragma unroll
@@ -145,17 +152,37 @@ __global__ void __launch_bounds__(kSortBlock) sort_scatter_kernel(const uint32_t
         status[(size_t)tile * 256u + dgt] = (exclusive + running) | kFlagPrefix;
     }
     digit_base[dgt] = s.hist[pass * 256 + dgt] + exclusive;
+    // exclusive scan of the tile's digit totals over the 256 digits -> start of each digit's run inside the tile
+    uint32_t incl = running;
+    for (int off = 1; off < 32; off <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= (uint32_t)off) incl += t;
+    }
+    if (lane == 31) warp_total[warp] = incl;
+    __syncthreads();
+    uint32_t before_warps = 0;
+    for (uint32_t w = 0; w < warp; w++) before_warps += warp_total[w];
+    digit_start[dgt] = before_warps + incl - running;
     __syncthreads();
 
+    // re-order the tile by digit in shared memory (stable), then stream it out run by run
 #pragma unroll
     for (int r = 0; r < kSortItems; r++) {
         uint32_t i = warp_base + r * 32u + lane;
         if (i < n) {
             uint32_t digit = (key[r] >> shift) & 255u;
-            uint32_t pos = digit_base[digit] + warp_hist[warp][digit] + rank[r];
-            keys_out[pos] = key[r];
-            values_out[pos] = val[r];
+            uint32_t local = digit_start[digit] + warp_hist[warp][digit] + rank[r];
+            stage_key[local] = key[r];
+            stage_val[local] = val[r];
         }
+    }
+    __syncthreads();
+    for (uint32_t j = threadIdx.x; j < tile_n; j += kSortBlock) {
+        const uint32_t k = stage_key[j];
+        const uint32_t digit = (k >> shift) & 255u;
+        const uint32_t pos = digit_base[digit] + (j - digit_start[digit]);
+        keys_out[pos] = k;
+        values_out[pos] = stage_val[j];
     }
 }
 

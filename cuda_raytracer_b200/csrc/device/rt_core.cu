@@ -40,6 +40,7 @@ struct rt_ctx {
     int32_t *d_order = nullptr;  // device build: BVH position -> file-order triangle id (inside d_build)
     std::vector<uint8_t> built_nodes;  // device build: the reference-layout nodes it produced (32 B each)
     double bvh_device_ms = 0;
+    double sort_device_ms = 0;
     int ray_count = 0, bounces = 0;
     float exposure = 0;
     int packed_nodes = 0, packed_depth = 0;
@@ -909,12 +910,24 @@ extern "C" int rt_sort_pairs(rt_ctx *ctx, uint32_t *keys, uint32_t *values, int3
     RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_keys[0], keys, (size_t)n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
     RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_vals[0], values, (size_t)n * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
     uint32_t *sk = nullptr, *sv = nullptr;
-    if ((rc = enqueue_sort(ctx, (const uint32_t *)count.p, (size_t)n, bits, false, &sk, &sv, nullptr)) != RT_OK) return rc;
+    cudaEvent_t e0, e1;
+    RT_CUDA(ctx, cudaEventCreate(&e0));
+    RT_CUDA(ctx, cudaEventCreate(&e1));
+    RT_CUDA(ctx, cudaEventRecord(e0, ctx->stream));
+    rc = enqueue_sort(ctx, (const uint32_t *)count.p, (size_t)n, bits, false, &sk, &sv, nullptr);
+    cudaEventRecord(e1, ctx->stream);
+    if (rc != RT_OK) { cudaEventDestroy(e0); cudaEventDestroy(e1); return rc; }
     RT_CUDA(ctx, cudaMemcpyAsync(keys, sk, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     RT_CUDA(ctx, cudaMemcpyAsync(values, sv, (size_t)n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    ctx->sort_device_ms = ms;
     return RT_OK;
 }
+extern "C" double rt_sort_device_ms(const rt_ctx *ctx) { return ctx ? ctx->sort_device_ms : 0.0; }
 
 // ---- device BVH build: inspection hooks ---------------------------------------------------------------------------
 extern "C" double rt_scene_bvh_device_ms(const rt_ctx *ctx) { return ctx ? ctx->bvh_device_ms : 0.0; }

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RT_API_VERSION 4
+#define RT_API_VERSION 5
 
 typedef enum rt_status {
     RT_OK = 0,
@@ -153,6 +153,8 @@ int rt_process_rays(rt_ctx *ctx, float *ray_data12, const uint32_t *seeds, int32
 /* The reorder pass on its own: stable LSD radix sort of (key, value) pairs on the low `bits` bits. Replaces
  * cub::DeviceRadixSort::SortPairs (raytracing.cu:194-195,240-246). In place on host arrays. */
 int rt_sort_pairs(rt_ctx *ctx, uint32_t *keys, uint32_t *values, int32_t n, int32_t bits);
+/* CUDA-event time of the sort kernels of the last rt_sort_pairs call (copies excluded), in milliseconds. */
+double rt_sort_device_ms(const rt_ctx *ctx);
 
 #ifdef __cplusplus
 }

@@ -178,6 +178,8 @@ def shim():
         L.ref_generate.argtypes = [C.c_void_p, f32p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int]
         L.ref_process.argtypes = [C.c_void_p, f32p, u32p, C.c_int]
         L.ref_render.argtypes = [C.c_void_p, C.c_int, f32p, C.POINTER(C.c_longlong)]
+        L.ref_cub_sort_pairs.argtypes = [u32p, u32p, C.c_int, C.c_int, C.POINTER(C.c_float)]
+        L.ref_cub_sort_pairs.restype = C.c_int
         L.ref_gpu_gen_seed.argtypes = [C.c_int, C.c_int]
         L.ref_gpu_gen_seed.restype = C.c_uint32
         L.ref_gpu_proc_seed.argtypes = [C.c_int, C.c_int]

@@ -19,6 +19,7 @@
 
 #include <cstring>
 #include <cstdio>
+#include <cub/device/device_radix_sort.cuh>
 
 static_assert(sizeof(RayData) == 48, "RayData layout");
 static_assert(sizeof(Triangle) == 48, "Triangle layout");
@@ -253,5 +254,43 @@ void ref_render(void *s, int seed_mode, float *out_rgb, long long *out_live)
 
 unsigned ref_gpu_gen_seed(int ray_index, int seed) { return gpu_gen_seed(ray_index, seed); }
 unsigned ref_gpu_proc_seed(int ray_index, int seed) { return gpu_proc_seed(ray_index, seed); }
+
+// The sort call the reference makes between bounces (raytracing.cu:194-195, 240-243): cub::DeviceRadixSort::SortPairs over
+// all 32 key bits of `n` (key, index) pairs. Returns the sorted pairs and the CUDA-event time of the best of `reps` calls
+// in milliseconds (device buffers, copies excluded). Used as the timing baseline of the product's own radix sort.
+int ref_cub_sort_pairs(unsigned *keys, unsigned *values, int n, int reps, float *best_ms)
+{
+    unsigned *k[2], *v[2];
+    for (int i = 0; i < 2; i++) {
+        if (cudaMalloc(&k[i], (size_t)n * 4) != cudaSuccess || cudaMalloc(&v[i], (size_t)n * 4) != cudaSuccess) return -1;
+    }
+    size_t temp_size = 0;
+    void *temp = nullptr;
+    cub::DeviceRadixSort::SortPairs(nullptr, temp_size, k[0], k[1], v[0], v[1], n);
+    if (cudaMalloc(&temp, temp_size) != cudaSuccess) return -1;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    float best = 1e30f;
+    for (int r = 0; r < reps; r++) {
+        cudaMemcpy(k[0], keys, (size_t)n * 4, cudaMemcpyHostToDevice);
+        cudaMemcpy(v[0], values, (size_t)n * 4, cudaMemcpyHostToDevice);
+        cudaEventRecord(e0);
+        cub::DeviceRadixSort::SortPairs(temp, temp_size, k[0], k[1], v[0], v[1], n);
+        cudaEventRecord(e1);
+        if (cudaEventSynchronize(e1) != cudaSuccess) return -2;
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (ms < best) best = ms;
+    }
+    cudaMemcpy(keys, k[1], (size_t)n * 4, cudaMemcpyDeviceToHost);
+    cudaMemcpy(values, v[1], (size_t)n * 4, cudaMemcpyDeviceToHost);
+    for (int i = 0; i < 2; i++) { cudaFree(k[i]); cudaFree(v[i]); }
+    cudaFree(temp);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    if (best_ms) *best_ms = best;
+    return cudaGetLastError() == cudaSuccess ? 0 : -3;
+}
 
 }  // extern "C"
