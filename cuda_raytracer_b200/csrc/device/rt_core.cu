@@ -312,7 +312,19 @@ int build_bvh_on_device(rt_ctx *ctx, const rt_scene_desc *s, int max_depth)
     if (n > 0) iota_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(order_a, n);
 
     int level_count = 1, node_count = 1;
+    const bool trace_levels = std::getenv("RT_BUILD_TRACE") != nullptr;  // per-level times on stderr (tuning aid)
+    std::vector<cudaEvent_t> marks;
+    std::vector<int> sizes;
+    auto mark = [&]() {
+        if (!trace_levels) return;
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        cudaEventRecord(e, ctx->stream);
+        marks.push_back(e);
+    };
+    mark();
     for (int level = 0; level_count > 0 && level <= max_depth; level++) {
+        sizes.push_back(level_count);
         BuildArgs a{};
         a.tris = static_cast<const BuildTri *>(ctx->d_raw);
         a.nodes = nodes;
@@ -331,12 +343,26 @@ int build_bvh_on_device(rt_ctx *ctx, const rt_scene_desc *s, int max_depth)
         node_count = c[0];
         level_count = c[1];
         RT_CUDA(ctx, cudaMemsetAsync(counters + 1, 0, sizeof(int32_t), ctx->stream));
+        mark();
     }
     RT_CUDA(ctx, cudaGetLastError());
     ctx->built_nodes.resize((size_t)node_count * sizeof(BuildNode));
     RT_CUDA(ctx, cudaMemcpyAsync(ctx->built_nodes.data(), nodes, ctx->built_nodes.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    mark();
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
     RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (trace_levels) {
+        float t0 = 0;
+        cudaEventElapsedTime(&t0, ctx->ev_start, marks[0]);
+        std::fprintf(stderr, "bvh build: %d triangles, copy-in %.3f ms\n", n, t0);
+        for (size_t i = 0; i + 1 < marks.size(); i++) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, marks[i], marks[i + 1]);
+            if (i < sizes.size()) std::fprintf(stderr, "  level %2zu: %7d nodes %8.3f ms\n", i, sizes[i], ms);
+            else std::fprintf(stderr, "  nodes to host: %.3f ms\n", ms);
+        }
+        for (cudaEvent_t e : marks) cudaEventDestroy(e);
+    }
     float ms = 0;
     RT_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_start, ctx->ev_stop));
     ctx->bvh_device_ms = ms;

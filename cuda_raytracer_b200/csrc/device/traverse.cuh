@@ -176,18 +176,25 @@ constexpr int kStackTop = RT_STACK_TOP;  // entries per thread kept in shared me
 // 8 B = 8 KB per CTA leaves the L1 to the BVH, unlike a full-depth shared stack (SmemStack).
 template <int BLOCK>
 struct HybridStack {
-    uint2 *top;  // &smem[0][threadIdx.x]
+    // shared-window address of smem[0][threadIdx.x], taken once: through a generic pointer the compiler re-derives the
+    // window base (S2R SR_CgaCtaId + 2 integer ops) at every push and pop
+    uint32_t top;
     uint2 deep[kStackDepth - kStackTop > 0 ? kStackDepth - kStackTop : 1];
-    __device__ __forceinline__ explicit HybridStack(uint2 *smem) : top(smem + threadIdx.x) {}
+    __device__ __forceinline__ explicit HybridStack(uint2 *smem) : top((uint32_t)__cvta_generic_to_shared(smem + threadIdx.x)) {}
     __device__ __forceinline__ void push(int sp, uint32_t r, float d)
     {
-        const uint2 v = make_uint2(r, __float_as_uint(d));
-        if (sp < kStackTop) top[sp * BLOCK] = v;
-        else deep[sp - kStackTop] = v;
+        if (sp < kStackTop)
+            asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(top + (uint32_t)sp * (BLOCK * 8u)), "r"(r), "r"(__float_as_uint(d)));
+        else
+            deep[sp - kStackTop] = make_uint2(r, __float_as_uint(d));
     }
     __device__ __forceinline__ void get(int sp, uint32_t &r, float &d) const
     {
-        const uint2 v = sp < kStackTop ? top[sp * BLOCK] : deep[sp - kStackTop];
+        uint2 v;
+        if (sp < kStackTop)
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(top + (uint32_t)sp * (BLOCK * 8u)));
+        else
+            v = deep[sp - kStackTop];
         r = v.x;
         d = __uint_as_float(v.y);
     }
