@@ -15,13 +15,16 @@
 // closest-hit results cannot see. tests/test_gpu_bvh_build.py checks both statements.
 #pragma once
 
+#include <cooperative_groups.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
 namespace rtd {
 
-constexpr int kBuildBlock = 256;
-constexpr int kBuildWarps = kBuildBlock / 32;
+constexpr int kBuildBlock = 256;     // one CTA per node: the many small nodes of the lower levels
+constexpr int kBuildBigBlock = 512;  // CTAs of a cluster working on one large node
+constexpr int kBuildCluster = 8;     // portable cluster size
+constexpr int kBuildBigNode = 2048;  // nodes with at least this many triangles go to a cluster
 constexpr int kBins = 8;
 
 struct BuildNode {  // the reference's 32-byte node (scene.cuh:82-100)
@@ -42,9 +45,10 @@ struct BuildArgs {
     const int32_t *order_in;   // triangle ids of the ranges of this level's nodes
     int32_t *order_out;        // partitions of the nodes that split
     int32_t *order_final;      // ranges of the nodes that became leaves
-    const int32_t *level_nodes;  // node ids of this level
-    int32_t *next_nodes;         // node ids of the next level
-    int32_t *counters;           // [0] nodes allocated, [1] size of the next level
+    const int32_t *level_small, *level_big;  // node ids of this level: one CTA each / one cluster each
+    int32_t *next_small, *next_big;          // node ids of the next level, by size class
+    int32_t *counters;                       // [0] nodes allocated, [1] next level's small nodes, [2] its big nodes
+    int32_t big_node_min;
     int32_t level;
     int32_t max_depth;
 };
@@ -74,32 +78,79 @@ __device__ __forceinline__ float warp_max(float v)
     return v;
 }
 
-__global__ void __launch_bounds__(kBuildBlock) bvh_level_kernel(const BuildArgs a)
+// One node per CTA (CLUSTER == 1) or per thread-block cluster (CLUSTER CTAs, each owning a contiguous chunk of the node's
+// range): the top levels hold a handful of nodes with 10^4-10^5 triangles each, and one CTA walking such a range was 70 % of
+// the whole build. Partial bounds, bins and left-counts of the CTAs are combined through distributed shared memory; every
+// CTA of the cluster then takes the same decision from the same merged data (min / max / integer sums: order-free), so
+// nothing has to be broadcast back.
+template <int CLUSTER>
+__device__ __forceinline__ void group_sync()
 {
-    __shared__ float red[kBuildWarps][12];                   // per-warp partial bounds
-    __shared__ float node_lo[3], node_hi[3], c_min[3], c_max[3];
-    __shared__ int32_t bin_lo[kBuildWarps][3][kBins][3], bin_hi[kBuildWarps][3][kBins][3];  // ordered-int boxes per warp
-    __shared__ int32_t bin_count[kBuildWarps][3][kBins];
-    __shared__ int32_t split_axis, left_total;
-    __shared__ float split_position;
-    __shared__ int32_t warp_left[kBuildWarps];
+    if (CLUSTER > 1) cooperative_groups::this_cluster().sync();
+    else __syncthreads();
+}
+template <int CLUSTER, class T>
+__device__ __forceinline__ const T *peer(const T *p, int rank)
+{
+    if (CLUSTER > 1) return cooperative_groups::this_cluster().map_shared_rank(const_cast<T *>(p), rank);
+    return p;
+}
 
-    const int node_id = a.level_nodes[blockIdx.x];
+struct TriData {  // one build-form triangle, three 16-byte loads
+    float4 a, b, c;  // a = p1.xyz p2.x, b = p2.yz p3.xy, c = p3.z centroid.xyz
+    __device__ __forceinline__ float lo(int k) const
+    {
+        return k == 0 ? fminf(a.x, fminf(a.w, b.z)) : k == 1 ? fminf(a.y, fminf(b.x, b.w)) : fminf(a.z, fminf(b.y, c.x));
+    }
+    __device__ __forceinline__ float hi(int k) const
+    {
+        return k == 0 ? fmaxf(a.x, fmaxf(a.w, b.z)) : k == 1 ? fmaxf(a.y, fmaxf(b.x, b.w)) : fmaxf(a.z, fmaxf(b.y, c.x));
+    }
+    __device__ __forceinline__ float centroid(int k) const { return k == 0 ? c.y : k == 1 ? c.z : c.w; }
+};
+__device__ __forceinline__ TriData load_tri(const BuildTri *tris, int id)
+{
+    const float4 *p = reinterpret_cast<const float4 *>(tris + id);
+    return TriData{__ldg(p), __ldg(p + 1), __ldg(p + 2)};
+}
+__device__ __forceinline__ float load_centroid(const BuildTri *tris, int id, int axis) { return __ldg(&tris[id].p[3][axis]); }
+
+template <int BLOCK, int CLUSTER>
+__global__ void __launch_bounds__(BLOCK) bvh_level_kernel(const BuildArgs a)
+{
+    constexpr int WARPS = BLOCK / 32;
+    __shared__ float red[WARPS][12];  // per-warp partial bounds
+    __shared__ float part[12];        // this CTA's partial bounds: lo, hi, centroid lo, centroid hi (read by the peers)
+    __shared__ float node_lo[3], node_hi[3], c_min[3], c_max[3];
+    __shared__ int32_t bin_lo[WARPS][3][kBins][3], bin_hi[WARPS][3][kBins][3];  // ordered-int boxes per warp
+    __shared__ int32_t bin_count[WARPS][3][kBins];
+    __shared__ int32_t cta_lo[3][kBins][3], cta_hi[3][kBins][3], cta_count[3][kBins];  // merged over the warps (read by the peers)
+    __shared__ float fin_lo[3][kBins][3], fin_hi[3][kBins][3];                          // merged over the cluster
+    __shared__ int32_t fin_count[3][kBins];
+    __shared__ int32_t split_axis, cta_left, left_total, left_before;
+    __shared__ float split_position;
+    __shared__ int32_t warp_left[WARPS];
+
+    const int rank = CLUSTER > 1 ? (int)cooperative_groups::this_cluster().block_rank() : 0;
+    const int node_id = (CLUSTER > 1 ? a.level_big : a.level_small)[blockIdx.x / CLUSTER];
     BuildNode &node = a.nodes[node_id];
     const int begin = node.child2, end = node.child1, count = end - begin;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // this CTA's chunk of the range: whole tiles of BLOCK triangles, in range order
+    const int per = ((count + CLUSTER - 1) / CLUSTER + BLOCK - 1) / BLOCK * BLOCK;
+    const int cb = min(end, begin + rank * per), ce = min(end, cb + per);
 
     // ---- A: node box over the vertices, centroid range per axis ----
     float lo[3] = {1e30f, 1e30f, 1e30f}, hi[3] = {-1e30f, -1e30f, -1e30f};
     float cl[3] = {1e30f, 1e30f, 1e30f}, ch[3] = {-1e30f, -1e30f, -1e30f};
-    for (int i = begin + threadIdx.x; i < end; i += kBuildBlock) {
-        const BuildTri &t = a.tris[a.order_in[i]];
+    for (int i = cb + threadIdx.x; i < ce; i += BLOCK) {
+        const TriData t = load_tri(a.tris, a.order_in[i]);
 #pragma unroll
         for (int k = 0; k < 3; k++) {
-            lo[k] = fminf(lo[k], fminf(t.p[0][k], fminf(t.p[1][k], t.p[2][k])));
-            hi[k] = fmaxf(hi[k], fmaxf(t.p[0][k], fmaxf(t.p[1][k], t.p[2][k])));
-            cl[k] = fminf(cl[k], t.p[3][k]);
-            ch[k] = fmaxf(ch[k], t.p[3][k]);
+            lo[k] = fminf(lo[k], t.lo(k));
+            hi[k] = fmaxf(hi[k], t.hi(k));
+            cl[k] = fminf(cl[k], t.centroid(k));
+            ch[k] = fmaxf(ch[k], t.centroid(k));
         }
     }
 #pragma unroll
@@ -112,23 +163,34 @@ __global__ void __launch_bounds__(kBuildBlock) bvh_level_kernel(const BuildArgs 
         for (int k = 0; k < 3; k++) { red[warp][k] = lo[k]; red[warp][3 + k] = hi[k]; red[warp][6 + k] = cl[k]; red[warp][9 + k] = ch[k]; }
     }
     __syncthreads();
-    if (threadIdx.x < 3) {
+    if (threadIdx.x < 12) {
         const int k = threadIdx.x;
-        float l = red[0][k], h = red[0][3 + k], c0 = red[0][6 + k], c1 = red[0][9 + k];
-        for (int w = 1; w < kBuildWarps; w++) {
-            l = fminf(l, red[w][k]); h = fmaxf(h, red[w][3 + k]);
-            c0 = fminf(c0, red[w][6 + k]); c1 = fmaxf(c1, red[w][9 + k]);
+        const bool is_min = k < 3 || (k >= 6 && k < 9);
+        float v = red[0][k];
+        for (int w = 1; w < WARPS; w++) v = is_min ? fminf(v, red[w][k]) : fmaxf(v, red[w][k]);
+        part[k] = v;
+    }
+    group_sync<CLUSTER>();
+    if (threadIdx.x < 12) {
+        const int k = threadIdx.x;
+        const bool is_min = k < 3 || (k >= 6 && k < 9);
+        float v = part[k];
+        for (int r = 0; r < CLUSTER; r++) {
+            const float o = peer<CLUSTER>(part, r)[k];
+            v = is_min ? fminf(v, o) : fmaxf(v, o);
         }
-        node_lo[k] = l; node_hi[k] = h; c_min[k] = c0; c_max[k] = c1;
-        node.lo[k] = l; node.hi[k] = h;
+        if (k < 3) { node_lo[k] = v; if (rank == 0) node.lo[k] = v; }
+        else if (k < 6) { node_hi[k - 3] = v; if (rank == 0) node.hi[k - 3] = v; }
+        else if (k < 9) c_min[k - 6] = v;
+        else c_max[k - 9] = v;
     }
     __syncthreads();
 
     bool leaf = count <= 4 || a.level >= a.max_depth;
 
-    // ---- B: per-warp bins, merged by the plane scan ----
+    // ---- B: per-warp bins -> per-CTA bins -> bins of the whole node ----
     if (!leaf) {
-        for (int i = threadIdx.x; i < kBuildWarps * 3 * kBins; i += kBuildBlock) {
+        for (int i = threadIdx.x; i < WARPS * 3 * kBins; i += BLOCK) {
             int32_t *bl = &bin_lo[0][0][0][0] + 3 * i, *bh = &bin_hi[0][0][0][0] + 3 * i;
             bl[0] = bl[1] = bl[2] = float_to_ordered(1e30f);
             bh[0] = bh[1] = bh[2] = float_to_ordered(-1e30f);
@@ -138,18 +200,18 @@ __global__ void __launch_bounds__(kBuildBlock) bvh_level_kernel(const BuildArgs 
         float to_bin[3];
 #pragma unroll
         for (int k = 0; k < 3; k++) to_bin[k] = __fdiv_rn((float)kBins, __fsub_rn(c_max[k], c_min[k]));
-        for (int i = begin + threadIdx.x; i < end; i += kBuildBlock) {
-            const BuildTri &t = a.tris[a.order_in[i]];
+        for (int i = cb + threadIdx.x; i < ce; i += BLOCK) {
+            const TriData t = load_tri(a.tris, a.order_in[i]);
             int32_t vlo[3], vhi[3];
 #pragma unroll
             for (int k = 0; k < 3; k++) {
-                vlo[k] = float_to_ordered(fminf(t.p[0][k], fminf(t.p[1][k], t.p[2][k])));
-                vhi[k] = float_to_ordered(fmaxf(t.p[0][k], fmaxf(t.p[1][k], t.p[2][k])));
+                vlo[k] = float_to_ordered(t.lo(k));
+                vhi[k] = float_to_ordered(t.hi(k));
             }
 #pragma unroll
             for (int axis = 0; axis < 3; axis++) {
                 if (c_min[axis] == c_max[axis]) continue;
-                const int b = min(kBins - 1, (int)__fmul_rn(__fsub_rn(t.p[3][axis], c_min[axis]), to_bin[axis]));
+                const int b = min(kBins - 1, (int)__fmul_rn(__fsub_rn(t.centroid(axis), c_min[axis]), to_bin[axis]));
                 atomicAdd(&bin_count[warp][axis][b], 1);
 #pragma unroll
                 for (int k = 0; k < 3; k++) {
@@ -157,6 +219,32 @@ __global__ void __launch_bounds__(kBuildBlock) bvh_level_kernel(const BuildArgs 
                     atomicMax(&bin_hi[warp][axis][b][k], vhi[k]);
                 }
             }
+        }
+        __syncthreads();
+        if (threadIdx.x < 3 * kBins * 3) {  // (axis, bin, component): merge the warps of this CTA
+            const int k = threadIdx.x % 3, ab = threadIdx.x / 3, axis = ab / kBins, b = ab % kBins;
+            int32_t l = bin_lo[0][axis][b][k], h = bin_hi[0][axis][b][k], c = bin_count[0][axis][b];
+            for (int w = 1; w < WARPS; w++) {
+                l = min(l, bin_lo[w][axis][b][k]);
+                h = max(h, bin_hi[w][axis][b][k]);
+                c += bin_count[w][axis][b];
+            }
+            cta_lo[axis][b][k] = l;
+            cta_hi[axis][b][k] = h;
+            if (k == 0) cta_count[axis][b] = c;
+        }
+        group_sync<CLUSTER>();
+        if (threadIdx.x < 3 * kBins * 3) {  // merge the CTAs of the cluster
+            const int k = threadIdx.x % 3, ab = threadIdx.x / 3, axis = ab / kBins, b = ab % kBins;
+            int32_t l = cta_lo[axis][b][k], h = cta_hi[axis][b][k], c = 0;
+            for (int r = 0; r < CLUSTER; r++) {
+                l = min(l, peer<CLUSTER>(&cta_lo[0][0][0], r)[threadIdx.x]);
+                h = max(h, peer<CLUSTER>(&cta_hi[0][0][0], r)[threadIdx.x]);
+                c += peer<CLUSTER>(&cta_count[0][0], r)[ab];
+            }
+            fin_lo[axis][b][k] = ordered_to_float(l);
+            fin_hi[axis][b][k] = ordered_to_float(h);
+            if (k == 0) fin_count[axis][b] = c;
         }
         __syncthreads();
 
@@ -167,30 +255,17 @@ __global__ void __launch_bounds__(kBuildBlock) bvh_level_kernel(const BuildArgs 
             int best_axis = -1;
             for (int axis = 0; axis < 3; axis++) {
                 if (c_min[axis] == c_max[axis]) continue;
-                float blo[kBins][3], bhi[kBins][3];
-                int bcount[kBins];
-                for (int b = 0; b < kBins; b++) {
-                    int c = 0;
-                    int32_t l[3] = {bin_lo[0][axis][b][0], bin_lo[0][axis][b][1], bin_lo[0][axis][b][2]};
-                    int32_t h[3] = {bin_hi[0][axis][b][0], bin_hi[0][axis][b][1], bin_hi[0][axis][b][2]};
-                    for (int w = 0; w < kBuildWarps; w++) {
-                        c += bin_count[w][axis][b];
-                        for (int k = 0; k < 3; k++) { l[k] = min(l[k], bin_lo[w][axis][b][k]); h[k] = max(h[k], bin_hi[w][axis][b][k]); }
-                    }
-                    bcount[b] = c;
-                    for (int k = 0; k < 3; k++) { blo[b][k] = ordered_to_float(l[k]); bhi[b][k] = ordered_to_float(h[k]); }
-                }
                 float area_left[kBins - 1], area_right[kBins - 1];
                 int count_left[kBins - 1];
                 float sl_lo[3] = {1e30f, 1e30f, 1e30f}, sl_hi[3] = {-1e30f, -1e30f, -1e30f};
                 float sr_lo[3] = {1e30f, 1e30f, 1e30f}, sr_hi[3] = {-1e30f, -1e30f, -1e30f};
                 int running = 0;
                 for (int k = 0; k + 1 < kBins; k++) {
-                    running += bcount[k];
+                    running += fin_count[axis][k];
                     count_left[k] = running;
                     for (int c = 0; c < 3; c++) {
-                        sl_lo[c] = fminf(sl_lo[c], blo[k][c]); sl_hi[c] = fmaxf(sl_hi[c], bhi[k][c]);
-                        sr_lo[c] = fminf(sr_lo[c], blo[kBins - 1 - k][c]); sr_hi[c] = fmaxf(sr_hi[c], bhi[kBins - 1 - k][c]);
+                        sl_lo[c] = fminf(sl_lo[c], fin_lo[axis][k][c]); sl_hi[c] = fmaxf(sl_hi[c], fin_hi[axis][k][c]);
+                        sr_lo[c] = fminf(sr_lo[c], fin_lo[axis][kBins - 1 - k][c]); sr_hi[c] = fmaxf(sr_hi[c], fin_hi[axis][kBins - 1 - k][c]);
                     }
                     area_left[k] = half_area_rn(sl_lo, sl_hi);
                     area_right[kBins - 2 - k] = half_area_rn(sr_lo, sr_hi);
@@ -218,32 +293,43 @@ __global__ void __launch_bounds__(kBuildBlock) bvh_level_kernel(const BuildArgs 
         const int axis = split_axis;
         const float position = split_position;
         int mine = 0;
-        for (int i = begin + threadIdx.x; i < end; i += kBuildBlock) mine += a.tris[a.order_in[i]].p[3][axis] < position ? 1 : 0;
+        for (int i = cb + threadIdx.x; i < ce; i += BLOCK) mine += load_centroid(a.tris, a.order_in[i], axis) < position ? 1 : 0;
         for (int off = 16; off > 0; off >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, off);
         if (lane == 0) warp_left[warp] = mine;
         __syncthreads();
         if (threadIdx.x == 0) {
             int total = 0;
-            for (int w = 0; w < kBuildWarps; w++) total += warp_left[w];
+            for (int w = 0; w < WARPS; w++) total += warp_left[w];
+            cta_left = total;
+        }
+        group_sync<CLUSTER>();
+        if (threadIdx.x == 0) {
+            int total = 0, before = 0;
+            for (int r = 0; r < CLUSTER; r++) {
+                const int c = *peer<CLUSTER>(&cta_left, r);
+                if (r < rank) before += c;
+                total += c;
+            }
             left_total = total;
+            left_before = before;
         }
         __syncthreads();
         const int n_left = left_total;
         leaf = n_left == 0 || n_left == count;
         if (!leaf) {
-            // tiles of kBuildBlock elements in order; running offsets keep both sides in input order
-            int left_done = 0, right_done = 0;
-            for (int base = begin; base < end; base += kBuildBlock) {
+            // tiles of BLOCK elements in range order; running offsets keep both sides in input order
+            int left_done = left_before, right_done = (cb - begin) - left_before;
+            for (int base = cb; base < ce; base += BLOCK) {
                 const int i = base + threadIdx.x;
-                const bool valid = i < end;
+                const bool valid = i < ce;
                 const int id = valid ? a.order_in[i] : 0;
-                const bool go_left = valid && a.tris[id].p[3][axis] < position;
+                const bool go_left = valid && load_centroid(a.tris, id, axis) < position;
                 const uint32_t ml = __ballot_sync(0xffffffffu, go_left), mv = __ballot_sync(0xffffffffu, valid);
                 __syncthreads();  // warp_left of the previous tile has been read
                 if (lane == 0) warp_left[warp] = __popc(ml) | (__popc(mv) << 16);
                 __syncthreads();
                 int l_before = 0, v_before = 0, l_tile = 0, v_tile = 0;
-                for (int w = 0; w < kBuildWarps; w++) {
+                for (int w = 0; w < WARPS; w++) {
                     const int l = warp_left[w] & 0xFFFF, v = warp_left[w] >> 16;
                     if (w < warp) { l_before += l; v_before += v; }
                     l_tile += l; v_tile += v;
@@ -257,28 +343,60 @@ __global__ void __launch_bounds__(kBuildBlock) bvh_level_kernel(const BuildArgs 
                 left_done += l_tile;
                 right_done += v_tile - l_tile;
             }
-            if (threadIdx.x == 0) {
+            if (rank == 0 && threadIdx.x == 0) {
                 const int pair = atomicAdd(&a.counters[0], 2);
                 BuildNode &l = a.nodes[pair], &r = a.nodes[pair + 1];
                 l.child2 = begin; l.child1 = begin + n_left;       // pending nodes carry their range, leaf convention
                 r.child2 = begin + n_left; r.child1 = end;
                 node.child1 = pair;
                 node.child2 = pair + 1;
-                const int slot = atomicAdd(&a.counters[1], 2);
-                a.next_nodes[slot] = pair;
-                a.next_nodes[slot + 1] = pair + 1;
+                const int counts[2] = {n_left, count - n_left};
+                for (int c = 0; c < 2; c++) {
+                    if (counts[c] >= a.big_node_min) a.next_big[atomicAdd(&a.counters[2], 1)] = pair + c;
+                    else a.next_small[atomicAdd(&a.counters[1], 1)] = pair + c;
+                }
             }
-            return;
         }
     }
     // leaf: its range is final
-    for (int i = begin + threadIdx.x; i < end; i += kBuildBlock) a.order_final[i] = a.order_in[i];
+    if (leaf)
+        for (int i = cb + threadIdx.x; i < ce; i += BLOCK) a.order_final[i] = a.order_in[i];
+    if (CLUSTER > 1) cooperative_groups::this_cluster().sync();  // a CTA's shared memory must outlive its peers' reads
 }
 
 __global__ void iota_kernel(int32_t *out, int32_t n)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) out[i] = i;
+}
+
+// Reference-layout nodes -> the tracer's 64-byte two-child records (device_scene.cuh), one thread per internal node.
+// Children are allocated in adjacent pairs (2k+1, 2k+2), and every pair belongs to exactly one internal node, so the pair
+// number k is a dense record index: record(node) = (node.child1 - 1) / 2, the root's record is 0. A leaf of more than
+// `max_leaf` triangles (depth limit or no useful plane) needs a chain of records: *needs_host is raised and the host
+// packer takes over.
+__global__ void pack_built_nodes_kernel(const BuildNode *__restrict__ nodes, int node_count, float4 *__restrict__ records,
+                                        uint32_t leaf_bit, int count_shift, int max_leaf, int32_t *needs_host)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= node_count) return;
+    const BuildNode n = nodes[i];
+    if (n.child2 <= n.child1) return;  // a leaf lives in its parent's record
+    float4 *rec = records + 4 * (size_t)((n.child1 - 1) >> 1);
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+        const BuildNode ch = nodes[n.child1 + c];
+        uint32_t ref;
+        if (ch.child2 > ch.child1) {
+            ref = (uint32_t)((ch.child1 - 1) >> 1);
+        } else {
+            const int count = ch.child1 - ch.child2;
+            if (count > max_leaf || count <= 0) { *needs_host = 1; return; }
+            ref = leaf_bit | ((uint32_t)count << count_shift) | (uint32_t)ch.child2;
+        }
+        rec[2 * c] = make_float4(ch.lo[0], ch.lo[1], ch.lo[2], ch.hi[0]);
+        rec[2 * c + 1] = make_float4(ch.hi[1], ch.hi[2], __uint_as_float(ref), 0.0f);
+    }
 }
 
 // Build form, file order -> 64-byte render-form records in BVH order (Scene::generate_bvh's tail, scene.cu:1029-1035:

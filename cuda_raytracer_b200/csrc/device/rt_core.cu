@@ -38,7 +38,10 @@ struct rt_ctx {
     void *d_build = nullptr;  // device BVH build scratch: nodes, order buffers, level lists, counters
     size_t cap_build = 0;
     int32_t *d_order = nullptr;  // device build: BVH position -> file-order triangle id (inside d_build)
-    std::vector<uint8_t> built_nodes;  // device build: the reference-layout nodes it produced (32 B each)
+    std::vector<uint8_t> built_nodes;  // device build: the reference-layout nodes it produced (32 B each), fetched on demand
+    int built_node_count = 0, built_levels = 0;
+    bool device_packed = false;  // the records in d_nodes were written by pack_built_nodes_kernel
+    float built_root[8] = {};    // the root node of a device-packed tree (box for the reorder key)
     double bvh_device_ms = 0;
     double sort_device_ms = 0;
     int ray_count = 0, bounces = 0;
@@ -287,7 +290,7 @@ int build_bvh_on_device(rt_ctx *ctx, const rt_scene_desc *s, int max_depth)
 {
     const int n = s->triangle_count;
     const size_t max_nodes = (size_t)2 * n + 2;
-    const size_t bytes = max_nodes * sizeof(BuildNode) + (size_t)3 * n * 4 + 2 * max_nodes * 4 + 64;
+    const size_t bytes = max_nodes * sizeof(BuildNode) + (size_t)3 * n * 4 + 4 * max_nodes * 4 + 64;
     int rc = reserve(ctx, &ctx->d_build, &ctx->cap_build, bytes);
     if (rc != RT_OK) return rc;
     if ((rc = reserve(ctx, &ctx->d_raw, &ctx->cap_raw, std::max<size_t>((size_t)n * 48, (size_t)s->env_width * s->env_height * 12))) != RT_OK) return rc;
@@ -295,8 +298,11 @@ int build_bvh_on_device(rt_ctx *ctx, const rt_scene_desc *s, int max_depth)
     BuildNode *nodes = reinterpret_cast<BuildNode *>(base);
     int32_t *order_a = reinterpret_cast<int32_t *>(base + max_nodes * sizeof(BuildNode));
     int32_t *order_b = order_a + n, *order_final = order_b + n;
-    int32_t *level_a = order_final + n, *level_b = level_a + max_nodes;
-    int32_t *counters = level_b + max_nodes;
+    int32_t *small_list[2] = {order_final + n, order_final + n + max_nodes};  // node ids per level, ping-pong, by size class
+    int32_t *big_list[2] = {small_list[1] + max_nodes, small_list[1] + 2 * max_nodes};
+    int32_t *counters = big_list[1] + max_nodes;
+    const char *big_env = std::getenv("RT_BUILD_BIG");
+    const int big_node_min = big_env ? std::max(1, std::atoi(big_env)) : kBuildBigNode;
     ctx->d_order = order_final;
 
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
@@ -305,13 +311,14 @@ int build_bvh_on_device(rt_ctx *ctx, const rt_scene_desc *s, int max_depth)
     for (int k = 0; k < 3; k++) { root.lo[k] = 1e30f; root.hi[k] = -1e30f; }
     root.child2 = 0;
     root.child1 = n;
-    const int32_t init[3] = {1, 0, 0};  // nodes allocated, next-level size, level_a[0] = root
+    const int32_t init[3] = {1, 0, 0};  // nodes allocated, next level's small / big nodes
+    const bool root_big = n >= big_node_min;
     RT_CUDA(ctx, cudaMemcpyAsync(nodes, &root, sizeof(root), cudaMemcpyHostToDevice, ctx->stream));
-    RT_CUDA(ctx, cudaMemcpyAsync(counters, init, 2 * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
-    RT_CUDA(ctx, cudaMemsetAsync(level_a, 0, sizeof(int32_t), ctx->stream));
+    RT_CUDA(ctx, cudaMemcpyAsync(counters, init, sizeof(init), cudaMemcpyHostToDevice, ctx->stream));
+    RT_CUDA(ctx, cudaMemsetAsync(root_big ? big_list[0] : small_list[0], 0, sizeof(int32_t), ctx->stream));  // the root's id
     if (n > 0) iota_kernel<<<(n + 255) / 256, 256, 0, ctx->stream>>>(order_a, n);
 
-    int level_count = 1, node_count = 1;
+    int small_count = root_big ? 0 : 1, big_count = root_big ? 1 : 0, node_count = 1;
     const bool trace_levels = std::getenv("RT_BUILD_TRACE") != nullptr;  // per-level times on stderr (tuning aid)
     std::vector<cudaEvent_t> marks;
     std::vector<int> sizes;
@@ -323,34 +330,72 @@ int build_bvh_on_device(rt_ctx *ctx, const rt_scene_desc *s, int max_depth)
         marks.push_back(e);
     };
     mark();
-    for (int level = 0; level_count > 0 && level <= max_depth; level++) {
-        sizes.push_back(level_count);
+    for (int level = 0; small_count + big_count > 0 && level <= max_depth; level++) {
+        sizes.push_back(small_count + big_count);
         BuildArgs a{};
         a.tris = static_cast<const BuildTri *>(ctx->d_raw);
         a.nodes = nodes;
         a.order_in = (level & 1) ? order_b : order_a;
         a.order_out = (level & 1) ? order_a : order_b;
         a.order_final = order_final;
-        a.level_nodes = (level & 1) ? level_b : level_a;
-        a.next_nodes = (level & 1) ? level_a : level_b;
+        a.level_small = small_list[level & 1];
+        a.level_big = big_list[level & 1];
+        a.next_small = small_list[(level & 1) ^ 1];
+        a.next_big = big_list[(level & 1) ^ 1];
         a.counters = counters;
         a.level = level;
         a.max_depth = max_depth;
-        bvh_level_kernel<<<level_count, kBuildBlock, 0, ctx->stream>>>(a);
-        int32_t c[2];
+        a.big_node_min = big_node_min;
+        if (big_count > 0) {  // one thread-block cluster per node
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3((unsigned)big_count * kBuildCluster);
+            cfg.blockDim = dim3(kBuildBigBlock);
+            cfg.stream = ctx->stream;
+            cudaLaunchAttribute attr{};
+            attr.id = cudaLaunchAttributeClusterDimension;
+            attr.val.clusterDim.x = kBuildCluster;
+            attr.val.clusterDim.y = 1;
+            attr.val.clusterDim.z = 1;
+            cfg.attrs = &attr;
+            cfg.numAttrs = 1;
+            RT_CUDA(ctx, cudaLaunchKernelEx(&cfg, bvh_level_kernel<kBuildBigBlock, kBuildCluster>, a));
+        }
+        if (small_count > 0) bvh_level_kernel<kBuildBlock, 1><<<small_count, kBuildBlock, 0, ctx->stream>>>(a);
+        int32_t c[3];
         RT_CUDA(ctx, cudaMemcpyAsync(c, counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
         RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         node_count = c[0];
-        level_count = c[1];
-        RT_CUDA(ctx, cudaMemsetAsync(counters + 1, 0, sizeof(int32_t), ctx->stream));
+        small_count = c[1];
+        big_count = c[2];
+        RT_CUDA(ctx, cudaMemsetAsync(counters + 1, 0, 2 * sizeof(int32_t), ctx->stream));
         mark();
     }
     RT_CUDA(ctx, cudaGetLastError());
-    ctx->built_nodes.resize((size_t)node_count * sizeof(BuildNode));
-    RT_CUDA(ctx, cudaMemcpyAsync(ctx->built_nodes.data(), nodes, ctx->built_nodes.size(), cudaMemcpyDeviceToHost, ctx->stream));
-    mark();
-    RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
-    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->built_node_count = node_count;
+    ctx->built_levels = (int)sizes.size();
+    ctx->device_packed = false;
+    if (node_count >= 3) {  // pack on the device; the nodes stay there unless rt_scene_download_bvh asks for them
+        const int records = (node_count - 1) / 2;
+        if ((rc = reserve(ctx, &ctx->d_nodes, &ctx->cap_nodes, (size_t)records * 64)) != RT_OK) return rc;
+        pack_built_nodes_kernel<<<(node_count + 255) / 256, 256, 0, ctx->stream>>>(nodes, node_count, (float4 *)ctx->d_nodes, kLeafBit,
+                                                                                   kLeafCountShift, kMaxLeafTris, counters + 1);
+        int32_t needs_host = 0;
+        RT_CUDA(ctx, cudaMemcpyAsync(&needs_host, counters + 1, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        RT_CUDA(ctx, cudaMemcpyAsync(ctx->built_root, nodes, sizeof(BuildNode), cudaMemcpyDeviceToHost, ctx->stream));
+        mark();
+        RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
+        RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        ctx->device_packed = needs_host == 0;
+        ctx->packed_nodes = records;
+        ctx->packed_depth = ctx->built_levels;
+    }
+    if (!ctx->device_packed) {  // tiny tree or a leaf that needs a chain: the host packer works from the nodes
+        ctx->built_nodes.resize((size_t)node_count * sizeof(BuildNode));
+        RT_CUDA(ctx, cudaMemcpyAsync(ctx->built_nodes.data(), nodes, ctx->built_nodes.size(), cudaMemcpyDeviceToHost, ctx->stream));
+        mark();
+        RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
+        RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
     if (trace_levels) {
         float t0 = 0;
         cudaEventElapsedTime(&t0, ctx->ev_start, marks[0]);
@@ -359,7 +404,7 @@ int build_bvh_on_device(rt_ctx *ctx, const rt_scene_desc *s, int max_depth)
             float ms = 0;
             cudaEventElapsedTime(&ms, marks[i], marks[i + 1]);
             if (i < sizes.size()) std::fprintf(stderr, "  level %2zu: %7d nodes %8.3f ms\n", i, sizes[i], ms);
-            else std::fprintf(stderr, "  nodes to host: %.3f ms\n", ms);
+            else std::fprintf(stderr, "  %s: %.3f ms\n", ctx->device_packed ? "pack records" : "nodes to host", ms);
         }
         for (cudaEvent_t e : marks) cudaEventDestroy(e);
     }
@@ -394,31 +439,38 @@ extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *s)
     if (rc != RT_OK) return rc;
 
     ctx->built_nodes.clear();
+    ctx->built_node_count = 0;
+    ctx->device_packed = false;
     ctx->d_order = nullptr;
     ctx->bvh_device_ms = 0;
     if (device_build && (rc = build_bvh_on_device(ctx, s, 30)) != RT_OK) return rc;  // MAX_BVH_DEPTH, scene.cu:10
     Packer packer;
-    packer.nodes = device_build ? reinterpret_cast<const RefNode *>(ctx->built_nodes.data()) : static_cast<const RefNode *>(s->bvh_nodes);
-    packer.run(device_build ? (int)(ctx->built_nodes.size() / sizeof(RefNode)) : s->bvh_node_count);
-    if (packer.max_depth > kStackDepth) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: BVH deeper than the traversal stack (32)");
-    ctx->packed_nodes = (int)packer.out.size();
-    ctx->packed_depth = packer.max_depth;
+    packer.nodes = reinterpret_cast<const RefNode *>(ctx->built_root);
+    if (!ctx->device_packed) {
+        packer.nodes = device_build ? reinterpret_cast<const RefNode *>(ctx->built_nodes.data()) : static_cast<const RefNode *>(s->bvh_nodes);
+        packer.run(device_build ? (int)(ctx->built_nodes.size() / sizeof(RefNode)) : s->bvh_node_count);
+        if (packer.max_depth > kStackDepth) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: BVH deeper than the traversal stack (32)");
+        ctx->packed_nodes = (int)packer.out.size();
+        ctx->packed_depth = packer.max_depth;
+    }
 
     const int prims = s->sphere_count + s->triangle_count;
     const size_t texels = (size_t)s->env_width * s->env_height;
     const size_t node_bytes = packer.out.size() * sizeof(PackedRecord);
     const size_t raw_tri = (size_t)s->triangle_count * 48, raw_env = texels * 12;
     // the previous upload's staging must have drained before it is overwritten
-    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (ctx->cap_stage < node_bytes) {
+    if (!ctx->device_packed) RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (!ctx->device_packed && ctx->cap_stage < node_bytes) {
         if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
         ctx->h_stage = nullptr;
         ctx->cap_stage = 0;
         RT_CUDA(ctx, cudaMallocHost(&ctx->h_stage, std::max<size_t>(node_bytes, 64)));
         ctx->cap_stage = std::max<size_t>(node_bytes, 64);
     }
-    std::memcpy(ctx->h_stage, packer.out.data(), node_bytes);
-    if ((rc = upload(ctx, &ctx->d_nodes, &ctx->cap_nodes, ctx->h_stage, node_bytes)) != RT_OK) return rc;
+    if (!ctx->device_packed) {
+        std::memcpy(ctx->h_stage, packer.out.data(), node_bytes);
+        if ((rc = upload(ctx, &ctx->d_nodes, &ctx->cap_nodes, ctx->h_stage, node_bytes)) != RT_OK) return rc;
+    }
     if ((rc = upload(ctx, &ctx->d_materials, &ctx->cap_materials, s->materials, (size_t)s->material_count * 48)) != RT_OK) return rc;
     if ((rc = upload(ctx, &ctx->d_spheres, &ctx->cap_spheres, s->spheres, (size_t)s->sphere_count * 16)) != RT_OK) return rc;
     if ((rc = upload(ctx, &ctx->d_matidx, &ctx->cap_matidx, s->material_indices, (size_t)prims * sizeof(uint16_t))) != RT_OK) return rc;
@@ -962,9 +1014,15 @@ extern "C" int rt_scene_download_bvh(rt_ctx *ctx, void *nodes32, int32_t node_ca
                                      int32_t order_capacity)
 {
     if (!ctx || !node_count) return fail(ctx, RT_ERR_INVALID, "rt_scene_download_bvh: null argument");
-    if (!ctx->has_scene || ctx->built_nodes.empty()) return fail(ctx, RT_ERR_INVALID, "rt_scene_download_bvh: the BVH was not built on the device");
-    const int n = (int)(ctx->built_nodes.size() / sizeof(BuildNode));
+    if (!ctx->has_scene || ctx->built_node_count <= 0) return fail(ctx, RT_ERR_INVALID, "rt_scene_download_bvh: the BVH was not built on the device");
+    const int n = ctx->built_node_count;
     *node_count = n;
+    if (nodes32 && ctx->built_nodes.empty()) {  // packed on the device: the nodes are still in the build buffer
+        RT_CUDA(ctx, cudaSetDevice(ctx->device));
+        ctx->built_nodes.resize((size_t)n * sizeof(BuildNode));
+        RT_CUDA(ctx, cudaMemcpyAsync(ctx->built_nodes.data(), ctx->d_build, ctx->built_nodes.size(), cudaMemcpyDeviceToHost, ctx->stream));
+        RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
     if (nodes32) {
         if (node_capacity < n) return fail(ctx, RT_ERR_INVALID, "rt_scene_download_bvh: node buffer too small");
         std::memcpy(nodes32, ctx->built_nodes.data(), ctx->built_nodes.size());

@@ -118,7 +118,8 @@ int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *scene);
 /* After an upload with triangles_form == 1: the tree the device built, in the reference's 32-byte node layout (numbered
  * breadth-first), and order[i] = file-order id of the triangle at BVH position i. Either output may be NULL. */
 int rt_scene_download_bvh(rt_ctx *ctx, void *nodes32, int32_t node_capacity, int32_t *node_count, int32_t *order, int32_t order_capacity);
-/* CUDA-event time of that build (H2D of the triangles, all levels, D2H of the nodes), 0 if the host built the tree. */
+/* CUDA-event time of that build (H2D of the triangles, all levels, packing into the tracer's records), 0 if the host
+ * built the tree. */
 double rt_scene_bvh_device_ms(const rt_ctx *ctx);
 /* Change the image block without re-uploading geometry (width/height/ray_count/bounces/exposure + camera basis). */
 int rt_scene_set_image(rt_ctx *ctx, const rt_scene_desc *scene);

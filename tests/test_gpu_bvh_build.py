@@ -122,3 +122,28 @@ def test_images_agree_and_empty_scene_builds(renderer):
     with pytest.raises(rt.RtError):
         renderer.upload(rt.load_scene("cornell.scene", cwd=SCENES))
         renderer.download_bvh(32)  # host-built scene: nothing to download
+
+
+def test_oversized_leaves_fall_back_to_the_host_packer(renderer, tmp_path):
+    """Twenty coincident quads: no plane through their 40 triangles beats the leaf cost (scene.cu:959), so the tree holds a
+    leaf of 40 > 15 triangles. Device packing hands over to the host packer, which chains such leaves."""
+    pile = "quad white -100 50 -100 -100 50 100 100 50 100 100 50 -100\n" * 20
+    text = ("material light diffuse 0 0 0 specular 0 0 0 emit 20 20 20\nmaterial white diffuse 0.7 0.7 0.7\n"
+            "quad light -50 300 -50 -50 300 50 50 300 50 50 300 -50\n" + pile +
+            "quad white -500 0 -500 -500 0 500 500 0 500 500 0 -500\nquad white -300 0 200 -300 90 200 300 90 200 300 0 200\n"
+            "sky 0.3 0.4 0.6\ncamera position 0 150 -600 forward 0 -0.1 1 up 0 1 0 fov 40\nimage 64 48 40 6 1\n")
+    (tmp_path / "pile.scene").write_text(text)
+    host = rt.load_scene("pile.scene", cwd=str(tmp_path))
+    dev = rt.load_scene("pile.scene", use_bvh="device", cwd=str(tmp_path))
+    ha = host.arrays()
+    leaf = ha["bvh"]["child2"] <= ha["bvh"]["child1"]
+    assert (ha["bvh"]["child1"][leaf] - ha["bvh"]["child2"][leaf]).max() == 40
+    rays = scene_rays(oracle_arrays(host), 50_000, seed=7)
+    renderer.upload(host)
+    prim_h, t_h = renderer.trace_closest(rays, with_spheres=True, stats=True)
+    tests_h = renderer.last_stats.triangle_tests
+    renderer.upload(dev)
+    prim_d, t_d = renderer.trace_closest(rays, with_spheres=True, stats=True)
+    assert t_d.tobytes() == t_h.tobytes() and renderer.last_stats.triangle_tests == tests_h
+    nodes, order = renderer.download_bvh(len(dev.arrays()["triangles"]))
+    assert np.array_equal(_node_signatures(nodes), _node_signatures(ha["bvh"]))

@@ -9,7 +9,7 @@ SCENES = os.path.join(ROOT, "scenes")
 name = sys.argv[1] if len(sys.argv) > 1 else "lamp"
 w, h, spp, bounces = (int(v) for v in (sys.argv[2:6] if len(sys.argv) > 5 else (1000, 1000, 100, 10)))
 variants = sys.argv[6].split(",") if len(sys.argv) > 6 else ["nosort", "sort15", "sort24"]
-scene = rt.load_scene(name + ".scene", cwd=SCENES).set_image(w, h, spp, bounces)
+scene = rt.load_scene(name + ".scene", use_bvh="device" if "devbvh" in sys.argv else True, cwd=SCENES).set_image(w, h, spp, bounces)
 r = rt.Renderer(0)
 r.upload(scene)
 r.render_device(sort=False, pass_count=1)  # warm-up
