@@ -3,11 +3,14 @@
 // whitespace tokenizer with explicit error reporting instead of the reference's istream juggling.
 #include "host_scene.hpp"
 
+#include <algorithm>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
 #include <sstream>
+#include <thread>
 #include <unordered_map>
 
 #include "../../../include/rt_core.h"
@@ -60,17 +63,39 @@ TriRecord build_form(F3 a, F3 b, F3 c)
     return t;
 }
 
+// Whole file into memory with one read (the meshes are a few hundred KB each; per-face istream calls were most of the
+// load time of lamp.scene).
+std::vector<char> read_whole_file(const std::string &path, const char *what)
+{
+    std::FILE *f = std::fopen(path.c_str(), "rb");
+    if (!f) fail(RT_ERR_IO, std::string("cannot open ") + what + " file '" + path + "'");
+    std::vector<char> data;
+    if (std::fseek(f, 0, SEEK_END) == 0) {
+        const long size = std::ftell(f);
+        std::rewind(f);
+        if (size > 0) {
+            data.resize((size_t)size);
+            if (std::fread(data.data(), 1, data.size(), f) != data.size()) data.clear();
+        }
+    }
+    std::fclose(f);
+    return data;
+}
+
 // Binary little-endian PLY as exported for the bundled meshes (scene.cu:491-546): float vertex properties (the
 // first three are the position), faces as uint8 count + int32 indices, fan-triangulated.
 void read_ply(std::vector<TriRecord> &out, const std::string &path)
 {
-    std::ifstream file(path, std::ios::binary);
-    if (!file) fail(RT_ERR_IO, "cannot open PLY file '" + path + "'");
-    std::string line;
+    const std::vector<char> data = read_whole_file(path, "PLY");
+    const char *p = data.data(), *end = p + data.size();
     long vertex_count = -1, face_count = -1;
     int vertex_floats = 0;
     bool in_vertex = false, header_done = false;
-    for (int guard = 0; guard < 256 && std::getline(file, line); guard++) {
+    for (int guard = 0; guard < 256 && p < end; guard++) {
+        const char *nl = static_cast<const char *>(std::memchr(p, '\n', (size_t)(end - p)));
+        if (!nl) break;
+        std::string line(p, nl);
+        p = nl + 1;
         if (!line.empty() && line.back() == '\r') line.pop_back();
         if (line.rfind("element vertex", 0) == 0) { vertex_count = std::atol(line.c_str() + 14); in_vertex = true; }
         else if (line.rfind("element face", 0) == 0) { face_count = std::atol(line.c_str() + 12); in_vertex = false; }
@@ -81,21 +106,24 @@ void read_ply(std::vector<TriRecord> &out, const std::string &path)
     if (!header_done || vertex_count < 0 || face_count < 0 || vertex_floats < 3)
         fail(RT_ERR_IO, "unsupported PLY header in '" + path + "'");
 
-    std::vector<float> vertices((size_t)vertex_count * vertex_floats);
-    file.read(reinterpret_cast<char *>(vertices.data()), (std::streamsize)(vertices.size() * sizeof(float)));
-    if (!file) fail(RT_ERR_IO, "truncated PLY vertex block in '" + path + "'");
+    const size_t vertex_bytes = (size_t)vertex_count * vertex_floats * sizeof(float);
+    if ((size_t)(end - p) < vertex_bytes) fail(RT_ERR_IO, "truncated PLY vertex block in '" + path + "'");
+    const char *vertices = p;
+    p += vertex_bytes;
     auto position = [&](int32_t i) -> F3 {
         if (i < 0 || i >= vertex_count) fail(RT_ERR_IO, "PLY face index out of range in '" + path + "'");
-        const float *v = &vertices[(size_t)i * vertex_floats];
+        float v[3];
+        std::memcpy(v, vertices + (size_t)i * vertex_floats * sizeof(float), sizeof(v));  // the block is not 4-byte aligned
         return {v[0], v[1], v[2]};
     };
-    std::vector<int32_t> corner;
+    out.reserve(out.size() + (size_t)face_count);
+    int32_t corner[256];
     for (long f = 0; f < face_count; f++) {
-        int n = file.get();
-        if (n == EOF) fail(RT_ERR_IO, "truncated PLY face block in '" + path + "'");
-        corner.resize((size_t)n);
-        file.read(reinterpret_cast<char *>(corner.data()), (std::streamsize)(sizeof(int32_t) * corner.size()));
-        if (!file) fail(RT_ERR_IO, "truncated PLY face block in '" + path + "'");
+        if (p >= end) fail(RT_ERR_IO, "truncated PLY face block in '" + path + "'");
+        const int n = (unsigned char)*p++;
+        if ((size_t)(end - p) < sizeof(int32_t) * (size_t)n) fail(RT_ERR_IO, "truncated PLY face block in '" + path + "'");
+        std::memcpy(corner, p, sizeof(int32_t) * (size_t)n);
+        p += sizeof(int32_t) * (size_t)n;
         for (int k = 2; k < n; k++) out.push_back(build_form(position(corner[0]), position(corner[k - 1]), position(corner[k])));
     }
 }
@@ -153,6 +181,17 @@ void load_scene_file(HostScene &scene, const char *path, int use_bvh, bool verbo
 
     std::unordered_map<std::string, uint16_t> material_ids;
     std::vector<uint16_t> sphere_materials, triangle_materials;
+    // `ply` lines are decoded after the parse, several files at a time; `at` is where the mesh goes in the list of the
+    // triangles written inline (triangle / quad), so the final order is the file's order, as in the reference
+    struct PlyJob {
+        std::string path;
+        uint16_t material;
+        size_t at;
+        std::vector<TriRecord> triangles;
+        int status = RT_OK;
+        std::string error;
+    };
+    std::vector<PlyJob> jobs;
     auto material_of = [&](const std::string &name, int line_no) -> uint16_t {
         auto it = material_ids.find(name);
         if (it == material_ids.end())
@@ -209,10 +248,11 @@ void load_scene_file(HostScene &scene, const char *path, int use_bvh, bool verbo
             triangle_materials.push_back(m);
             triangle_materials.push_back(m);
         } else if (cmd == "ply") {
-            uint16_t m = material_of(t.word(), line_no);
-            size_t before = scene.triangles.size();
-            read_ply(scene.triangles, t.word());
-            triangle_materials.insert(triangle_materials.end(), scene.triangles.size() - before, m);
+            PlyJob job;
+            job.material = material_of(t.word(), line_no);
+            job.path = t.word();
+            job.at = scene.triangles.size();
+            jobs.push_back(std::move(job));
         } else if (cmd == "image") {
             scene.width = t.integer();
             scene.height = t.integer();
@@ -220,6 +260,43 @@ void load_scene_file(HostScene &scene, const char *path, int use_bvh, bool verbo
             scene.bounces = t.integer();
             scene.exposure = t.number();
         }  // unknown commands are ignored, as in the reference
+    }
+
+    if (!jobs.empty()) {
+        std::atomic<size_t> next_job{0};
+        auto worker = [&]() {
+            for (size_t j; (j = next_job.fetch_add(1)) < jobs.size();) {
+                try { read_ply(jobs[j].triangles, jobs[j].path); }
+                catch (const LoadError &e) { jobs[j].status = e.status; jobs[j].error = e.message; }
+            }
+        };
+        const size_t n_threads = std::min<size_t>({jobs.size(), (size_t)std::max(1u, std::thread::hardware_concurrency()), (size_t)16});
+        std::vector<std::thread> pool;
+        for (size_t i = 1; i < n_threads; i++) pool.emplace_back(worker);
+        worker();
+        for (std::thread &th : pool) th.join();
+        for (const PlyJob &job : jobs)  // the first failure in file order, as a sequential load would report it
+            if (job.status != RT_OK) fail(job.status, job.error);
+        std::vector<TriRecord> merged;
+        std::vector<uint16_t> merged_materials;
+        size_t total = scene.triangles.size();
+        for (const PlyJob &job : jobs) total += job.triangles.size();
+        merged.reserve(total);
+        merged_materials.reserve(total);
+        size_t inline_done = 0;
+        auto take_inline = [&](size_t upto) {
+            merged.insert(merged.end(), scene.triangles.begin() + inline_done, scene.triangles.begin() + upto);
+            merged_materials.insert(merged_materials.end(), triangle_materials.begin() + inline_done, triangle_materials.begin() + upto);
+            inline_done = upto;
+        };
+        for (const PlyJob &job : jobs) {
+            take_inline(job.at);
+            merged.insert(merged.end(), job.triangles.begin(), job.triangles.end());
+            merged_materials.insert(merged_materials.end(), job.triangles.size(), job.material);
+        }
+        take_inline(scene.triangles.size());
+        scene.triangles.swap(merged);
+        triangle_materials.swap(merged_materials);
     }
 
     scene.material_indices = sphere_materials;
