@@ -1,0 +1,90 @@
+"""GPU tests at BASELINE.json's full sizes (lamp.scene at 3840x2160, R = 165,888,000 rays per pass), where the oracle is
+far too slow to be the checker: size-independent properties of the path instead.
+
+  * additivity: passes are independent units (raytracing.cu:222-254), so disjoint pass ranges sum to the whole frame and
+    their live-ray counters add up exactly (integer);
+  * wave invariance: tracing several passes together keeps every pass's own seeds -> same counters, same image up to float
+    summation order;
+  * reorder invariance: seeds follow the ray, not its slot -> sorting on or off, same counters;
+  * the first bounce of a 4K pass, ray for ray, on the host-built and the device-built tree: bit-identical distances;
+  * the radix sort on R pairs: sorted, a permutation, stable.
+"""
+import numpy as np
+import pytest
+
+import cuda_raytracer_b200 as rt
+from util import SCENES
+
+pytestmark = pytest.mark.gpu
+W, H = 3840, 2160
+
+
+@pytest.fixture(scope="module")
+def renderer():
+    r = rt.Renderer(0)
+    yield r
+    r.close()
+
+
+def test_lamp_4k_additivity_and_wave_invariance(renderer):
+    scene = rt.load_scene("lamp.scene", cwd=SCENES).set_image(W, H, 40, 10, 1.0)  # two full passes of 20 spp
+    renderer.upload(scene)
+    whole = renderer.render(sort=False, pass_group=2)
+    st = renderer.last_stats
+    n_whole, primary = st.live_ray_bounces, st.primary_rays
+    assert primary == W * H * 40 and st.passes == 2
+    assert np.isfinite(whole).all() and whole.min() >= 0.0
+    parts, counts = [], []
+    for first in (0, 1):
+        parts.append(renderer.render(sort=False, pass_group=1, pass_first=first, pass_count=1))
+        counts.append(renderer.last_stats.live_ray_bounces)
+        assert renderer.last_stats.primary_rays == W * H * 20
+    assert sum(counts) == n_whole  # integer, exact
+    assert 2.0 < n_whole / primary < 2.7  # lamp: 2.32 live ray-bounces per primary ray (SURVEY §8d measured 2.3-3.0 at low res)
+    total = parts[0].astype(np.float64) + parts[1]
+    # per pixel: atomics add the same 40 contributions in another order
+    assert np.allclose(total, whole, rtol=2e-4, atol=2e-4 * whole.mean())
+    # checksum of checksums: row sums of the parts against row sums of the whole
+    assert np.allclose(total.sum(axis=(1, 2)), whole.astype(np.float64).sum(axis=(1, 2)), rtol=1e-6)
+    sorted_img = renderer.render(sort=True, pass_group=1, pass_first=1, pass_count=1)
+    assert renderer.last_stats.live_ray_bounces == counts[1] and renderer.last_stats.sorted_pairs > 0
+    assert np.allclose(sorted_img, parts[1], rtol=2e-4, atol=2e-4 * whole.mean())
+
+
+def test_first_bounce_of_a_4k_pass_on_both_trees(renderer):
+    """8.3 M primary rays (one per pixel) through trace_closest on the host-built and the device-built BVH."""
+    host = rt.load_scene("lamp.scene", cwd=SCENES).set_image(W, H, 1, 1, 1.0)
+    dev = rt.load_scene("lamp.scene", use_bvh="device", cwd=SCENES).set_image(W, H, 1, 1, 1.0)
+    renderer.upload(host)
+    rays = renderer.generate_rays(1, 0, W * H, 3)[:, :6].copy()
+    assert rays.shape == (W * H, 6)
+    prim_h, t_h = renderer.trace_closest(rays, with_spheres=True)
+    renderer.upload(dev)
+    prim_d, t_d = renderer.trace_closest(rays, with_spheres=True)
+    assert t_h.tobytes() == t_d.tobytes()
+    hit = prim_h >= 0
+    assert ((prim_d >= 0) == hit).all() and 0.2 < hit.mean() < 1.0
+    t = t_h[hit]
+    assert np.isfinite(t).all() and (t > 0.005).all()
+    # a second call returns the same bits: the persistent tracer's dynamic ray fetch does not leak into results
+    prim_d2, t_d2 = renderer.trace_closest(rays, with_spheres=True)
+    assert t_d2.tobytes() == t_d.tobytes() and (prim_d2 == prim_d).all()
+
+
+@pytest.mark.parametrize("bits", [15, 32])
+def test_radix_sort_at_one_pass_of_4k_rays(renderer, bits):
+    n = W * H * 20  # R at the headline configuration
+    rs = np.random.RandomState(bits)
+    keys = rs.randint(0, 2 ** 32, size=n, dtype=np.uint64).astype(np.uint32)
+    if bits < 32:
+        keys &= np.uint32((1 << bits) - 1)
+    keys[: n // 4] = keys[0]  # a long run of equal keys
+    vals = np.arange(n, dtype=np.uint32)
+    k, v = renderer.sort_pairs(keys, vals, bits)
+    assert (k[1:] >= k[:-1]).all(), "sorted"
+    assert (keys[v] == k).all(), "every output pair is an input pair"
+    seen = np.zeros(n, np.uint8)
+    seen[v] = 1
+    assert seen.all(), "permutation"
+    same = k[1:] == k[:-1]
+    assert (v[1:][same] > v[:-1][same]).all(), "stable: equal keys keep their input order"

@@ -1,0 +1,6 @@
+#!/bin/bash
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_fullsize.py -m gpu -x -q --durations=5 > gpurun_out/pytest_full.log 2>&1; echo "rc=$?" >> gpurun_out/pytest_full.log
+BCMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-ref-gpu"
+$BCMD > gpurun_out/bench_plain.json 2> gpurun_out/bench_plain.err && timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file gpurun_out/r1e_launches_bench.csv $BCMD > gpurun_out/ncu_launch.log 2>&1
+echo "ncu rc=$?" >> gpurun_out/ncu_launch.log
