@@ -146,9 +146,9 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
 // IO policy:  bool load(uint32_t i, float3 &o, float3 &d, float &closest, int &prim)   false = nothing to trace
 //             void store(uint32_t i, float closest, int prim)
 constexpr uint32_t kDoneRef = 0xFFFFFFFFu;  // never a valid leaf ref: start would exceed the 2^27 triangle limit
-constexpr int kBatch = 96;                  // default: rays a warp claims per global atomic
-constexpr int kRefillBelow = 22;            // default: refill when fewer lanes than this still hold a ray
-constexpr int kNodeMin = 8;                 // default for TraceTuning::node_min
+constexpr int kBatch = 192;                 // default: rays a warp claims per global atomic
+constexpr int kRefillBelow = 16;           // default: refill when fewer lanes than this still hold a ray
+constexpr int kNodeMin = 12;                // default for TraceTuning::node_min
 struct TraceTuning {
     uint32_t batch;         // rays per claim; the kernel shrinks it when the bounce has fewer rays than batch x warps
     uint32_t refill_below;
