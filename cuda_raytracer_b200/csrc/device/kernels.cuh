@@ -135,11 +135,37 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
     }
     // whole CTAs iterate together: the compaction below reserves output slots once per CTA and iteration (a single
     // per-warp atomic on one counter was 50 % of this kernel's stall samples, profiles/r1b_split_lamp1k.md)
-    __shared__ uint32_t warp_count[kShadeBlock / 32];
-    __shared__ uint32_t block_base;
+    __shared__ uint32_t warp_count_buf[2][kShadeBlock / 32];  // double-buffered: two barriers per iteration instead of three
+    __shared__ uint32_t block_base_buf[2];
+    uint32_t parity = 0;
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t n_round = (n_in + kShadeBlock - 1u) / kShadeBlock * kShadeBlock;
-    for (uint32_t i = blockIdx.x * kShadeBlock + threadIdx.x; i < n_round; i += gridDim.x * kShadeBlock) {
+    // the queue entry and hit record of the NEXT iteration are requested before this one is shaded: the streams come from
+    // HBM (long-scoreboard stalls were the top stall reason of this kernel, profiles/r1e)
+    struct Fetched {
+        float4 ra, rb;
+        float2 rc, h;
+    };
+    auto fetch = [&](uint32_t i) {
+        Fetched f;
+        f.ra = f.rb = make_float4(0, 0, 0, 0);
+        f.rc = f.h = make_float2(0, 0);
+        if (i < n_in) {
+            if (!FIRST) {
+                const uint32_t slot = a.order ? __ldg(a.order + i) : i;
+                f.ra = __ldcs(a.in.qa + slot);
+                f.rb = __ldcs(a.in.qb + slot);
+                f.rc = __ldcs(a.in.qc + slot);
+            }
+            f.h = __ldcs(a.hits + i);
+        }
+        return f;
+    };
+    const uint32_t stride = gridDim.x * kShadeBlock;
+    Fetched next = fetch(blockIdx.x * kShadeBlock + threadIdx.x);
+    for (uint32_t i = blockIdx.x * kShadeBlock + threadIdx.x; i < n_round; i += stride) {
+        const Fetched cur = next;
+        next = fetch(i + stride);
         bool active = i < n_in;
         float3 o = f3(0, 0, 0), d = f3(0, 0, 1), T = f3(1, 1, 1);
         uint32_t id = i;
@@ -148,20 +174,17 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
                 const uint32_t g = id / a.pass_rays;
                 active = generate_ray(sc, id - g * a.pass_rays, a.rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d);
             } else {
-                const uint32_t slot = a.order ? __ldg(a.order + i) : i;
-                const float4 ra = __ldcs(a.in.qa + slot), rb = __ldcs(a.in.qb + slot);
-                const float2 rc = __ldcs(a.in.qc + slot);
-                o = f3(ra.x, ra.y, ra.z);
-                d = f3(ra.w, rb.x, rb.y);
-                T = f3(rb.z, rb.w, rc.x);
-                id = __float_as_uint(rc.y);
+                o = f3(cur.ra.x, cur.ra.y, cur.ra.z);
+                d = f3(cur.ra.w, cur.rb.x, cur.rb.y);
+                T = f3(cur.rb.z, cur.rb.w, cur.rc.x);
+                id = __float_as_uint(cur.rc.y);
             }
         }
         bool alive = false;
         float3 radiance = f3(0, 0, 0);
         uint32_t pixel = 0xFFFFFFFFu;
         if (active) {
-            const float2 h = __ldcs(a.hits + i);
+            const float2 h = cur.h;
             const float closest = h.x;
             const int prim = __float_as_int(h.y);
             const uint32_t g = id / a.pass_rays, index = id - g * a.pass_rays;  // pass of the wave, ray index inside it
@@ -176,6 +199,9 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
         }
         add_radiance_warp(a.framebuffer, pixel, radiance);
         if (write_out) {  // next-bounce compaction: survivors keep their order inside the CTA's contiguous output range
+            uint32_t *warp_count = warp_count_buf[parity];
+            uint32_t &block_base = block_base_buf[parity];
+            parity ^= 1u;
             const uint32_t mask = __ballot_sync(0xffffffffu, alive);
             if (lane == 0) warp_count[warp] = __popc(mask);
             __syncthreads();
@@ -197,7 +223,8 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
                 __stcs(a.out.qc + pos, make_float2(T.z, __uint_as_float(id)));
                 if (a.keys_out) a.keys_out[pos] = reorder_key(sc.key_min, sc.key_inv_extent, o, d, a.key_bits);
             }
-            __syncthreads();  // warp_count / block_base are rewritten by the next iteration
+            // no barrier here: the next iteration writes the other buffer, and this one is rewritten only after every
+            // thread has passed that iteration's first barrier
         }
     }
 }
