@@ -386,7 +386,7 @@ def main():
         "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{scene_name}.scene {w}x{h} {spp} spp {bounces} bounces (lamp-subset geometry, synthetic env map)",
-                   "passes": total_passes, "pass_spp": PASS_SPP, "pass_group": args.pass_group or "auto (free memory / 3)", "sort": int(sort), "parallelism": f"spp-split x{world} + NCCL reduce",
+                   "passes": total_passes, "pass_spp": PASS_SPP, "pass_group": args.pass_group or "auto (70 % of free memory)", "sort": int(sort), "parallelism": f"spp-split x{world} + NCCL reduce",
                    "l2": "inputs larger than L2: ray queues are %.1f GB per pass; the packed scene (%.0f MB) is L2-resident by nature"
                          % (w * h * PASS_SPP * 40 * 2 / 1e9, scene_bytes / 1e6)},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_s / args.steps * 1e3,

@@ -686,12 +686,12 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     if (rc != RT_OK) return rc;
     const size_t pass_rays_max = pixels * (size_t)std::min(pass_spp, std::max(1, ctx->ray_count));
     int max_group = opts.pass_group;
-    if (max_group <= 0) {  // auto: as many passes per wave as fit in a third of the free device memory (ids stay < 2^31)
+    if (max_group <= 0) {  // auto: as many passes per wave as fit in 70 % of the free device memory (ids stay < 2^31)
         size_t free_b = 0, total_b = 0;
         RT_CUDA(ctx, cudaMemGetInfo(&free_b, &total_b));
         const size_t have = ctx->queue_capacity * (size_t)(88 + (sort ? 16 : 0));  // already ours, so also "free"
         const size_t per_pass = pass_rays_max * (size_t)(88 + (sort ? 16 : 0));    // 2 x 40 B queues + 8 B hit (+ keys, permutation)
-        max_group = (int)std::max<size_t>(1, (free_b + have) / 3 / std::max<size_t>(1, per_pass));
+        max_group = (int)std::max<size_t>(1, (free_b + have) / 10 * 7 / std::max<size_t>(1, per_pass));
     }
     max_group = std::max(1, std::min({max_group, (int)kMaxPassGroup, pass_end - pass_first}));
     while (max_group > 1 && pass_rays_max * (size_t)max_group >= (1ull << 31)) max_group--;
