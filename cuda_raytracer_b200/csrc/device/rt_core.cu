@@ -695,7 +695,12 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     }
     max_group = std::max(1, std::min({max_group, (int)kMaxPassGroup, pass_end - pass_first}));
     while (max_group > 1 && pass_rays_max * (size_t)max_group >= (1ull << 31)) max_group--;
-    if ((rc = ensure_queues(ctx, pass_rays_max * (size_t)max_group, sort)) != RT_OK) return rc;
+    // the automatic wave size is a guess at what the allocator will grant: on an out-of-memory answer try smaller waves
+    while ((rc = ensure_queues(ctx, pass_rays_max * (size_t)max_group, sort)) == RT_ERR_NOMEM && opts.pass_group <= 0 && max_group > 1) {
+        cudaGetLastError();
+        max_group = (max_group + 1) / 2;
+    }
+    if (rc != RT_OK) return rc;
 
     int grid = 0;
     if ((rc = trace_grid_size(ctx, &grid)) != RT_OK) return rc;
