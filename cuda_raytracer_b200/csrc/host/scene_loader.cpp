@@ -268,6 +268,7 @@ void load_scene_file(HostScene &scene, const char *path, int use_bvh, bool verbo
             for (size_t j; (j = next_job.fetch_add(1)) < jobs.size();) {
                 try { read_ply(jobs[j].triangles, jobs[j].path); }
                 catch (const LoadError &e) { jobs[j].status = e.status; jobs[j].error = e.message; }
+                catch (const std::exception &e) { jobs[j].status = RT_ERR_IO; jobs[j].error = "reading '" + jobs[j].path + "': " + e.what(); }
             }
         };
         const size_t n_threads = std::min<size_t>({jobs.size(), (size_t)std::max(1u, std::thread::hardware_concurrency()), (size_t)16});
