@@ -58,16 +58,17 @@ struct RayQueue {
 };
 
 // Per-pass device counters (zeroed by one memset per pass).
+constexpr int kMaxBounces = 256;  // the reference has no limit; these per-bounce counters need one
 struct PassCounters {
-    uint32_t cursor[33];  // work-fetch cursor of bounce b
-    uint32_t count[33];   // live rays entering bounce b (count[0] unused: known on the host)
+    uint32_t cursor[kMaxBounces + 1];  // work-fetch cursor of bounce b
+    uint32_t count[kMaxBounces + 1];   // live rays entering bounce b (count[0] unused: known on the host)
 };
 
 struct RenderTotals {
     unsigned long long live_ray_bounces;
     unsigned long long internal_visits;
     unsigned long long triangle_tests;
-    unsigned long long live_per_bounce[32];
+    unsigned long long live_per_bounce[32];  // bounces past the 32nd are added to the last entry
 };
 
 struct BounceArgs {

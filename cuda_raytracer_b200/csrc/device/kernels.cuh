@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
 
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         atomicAdd(&a.totals->live_ray_bounces, (unsigned long long)n_in);
-        atomicAdd(&a.totals->live_per_bounce[a.bounce], (unsigned long long)n_in);
+        atomicAdd(&a.totals->live_per_bounce[min(a.bounce, 31)], (unsigned long long)n_in);
     }
     // whole CTAs iterate together: the compaction below reserves output slots once per CTA and iteration (a single
     // per-warp atomic on one counter was 50 % of this kernel's stall samples, profiles/r1b_split_lamp1k.md)

@@ -203,8 +203,8 @@ void copy3(float *dst, const float *src) { dst[0] = src[0]; dst[1] = src[1]; dst
 
 int set_image_block(rt_ctx *ctx, const rt_scene_desc *s)
 {
-    if (s->width <= 0 || s->height <= 0 || s->ray_count < 0 || s->bounces < 0 || s->bounces > 32)
-        return fail(ctx, RT_ERR_INVALID, "image block: need width,height > 0, ray_count >= 0, 0 <= bounces <= 32");
+    if (s->width <= 0 || s->height <= 0 || s->ray_count < 0 || s->bounces < 0 || s->bounces > kMaxBounces)
+        return fail(ctx, RT_ERR_INVALID, "image block: need width,height > 0, ray_count >= 0, 0 <= bounces <= 256");
     DeviceScene &d = ctx->ds;
     d.width = s->width;
     d.height = s->height;
@@ -801,8 +801,8 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             float e_ms = 0;
             RT_CUDA(ctx, cudaEventElapsedTime(&e_ms, ctx->ev_pool[k], ctx->ev_pool[k + 1]));
             (ev_kind[k] == 0 ? stats->trace_ms : ev_kind[k] == 2 ? stats->shade_ms : stats->sort_ms) += e_ms;
-            if (ev_kind[k] == 0) stats->trace_ms_per_bounce[ev_bounce[k]] += e_ms;
-            if (ev_kind[k] == 2) stats->shade_ms_per_bounce[ev_bounce[k]] += e_ms;
+            if (ev_kind[k] == 0) stats->trace_ms_per_bounce[std::min(ev_bounce[k], 31)] += e_ms;
+            if (ev_kind[k] == 2) stats->shade_ms_per_bounce[std::min(ev_bounce[k], 31)] += e_ms;
         }
         stats->total_seconds = std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - wall0).count();
     }

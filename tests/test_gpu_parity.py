@@ -138,7 +138,8 @@ def test_process_step_vs_oracle(renderer, name):
 
 @pytest.mark.parametrize("name,w,h,spp,bounces", [
     ("cornell", 64, 64, 40, 10), ("cornell_plus", 64, 64, 40, 10), ("spheres", 64, 64, 40, 10),
-    ("teapot", 64, 48, 25, 10), ("glass_teapot", 64, 48, 25, 10), ("lamp", 64, 48, 25, 10)])
+    ("teapot", 64, 48, 25, 10), ("glass_teapot", 64, 48, 25, 10), ("lamp", 64, 48, 25, 10),
+    ("cornell_plus", 40, 32, 25, 48)])  # more bounces than the 32 per-bounce slots of rt_stats (the reference has no limit)
 def test_image_vs_oracle_matched_seeds(renderer, name, w, h, spp, bounces):
     scene, A = _setup(renderer, name, w, h, spp, bounces)
     want, ctr = oracle_render(A, seed_mode=1)
@@ -186,6 +187,14 @@ def test_pass_grouping_does_not_change_the_image(renderer):
     part = renderer.render(sort=False, pass_group=3, pass_first=1, pass_count=4)
     ref = renderer.render(sort=False, pass_group=1, pass_first=1, pass_count=4)
     assert np.allclose(part, ref, rtol=1e-4, atol=1e-4 * ref.mean())
+
+
+def test_bounce_limit_is_reported(renderer):
+    scene = load("cornell").set_image(16, 16, 1, 257, 1.0)
+    with pytest.raises(rt.RtError):
+        renderer.upload(scene)
+    renderer.upload(load("cornell").set_image(16, 16, 1, 256, 1.0))
+    assert np.isfinite(renderer.render(sort=True)).all()
 
 
 def test_edge_configs(renderer):
