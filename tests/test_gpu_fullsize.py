@@ -88,3 +88,20 @@ def test_radix_sort_at_one_pass_of_4k_rays(renderer, bits):
     assert seen.all(), "permutation"
     same = k[1:] == k[:-1]
     assert (v[1:][same] > v[:-1][same]).all(), "stable: equal keys keep their input order"
+
+
+def test_bloom_and_tonemap_bit_exact_at_4k(renderer):
+    """Output tail of a frame (raytracing.cu:21-74, 286-303, 360-392) on the real render of the 4K configuration: device
+    kernels against the oracle's host loops, sums and bytes bit-exact."""
+    import pyoracle as po
+    scene = rt.load_scene("lamp.scene", cwd=SCENES).set_image(W, H, 20, 10, 1.0)
+    renderer.upload(scene)
+    sums = renderer.render(sort=False).copy()
+    assert (sums.reshape(-1, 3) @ np.array([0.2126, 0.7152, 0.0722], np.float32) > 0.7 * 20).any(), "some pixels must bloom"
+    want = sums.copy()
+    po.port().oracle_bloom(want.reshape(-1), W, H, 20)
+    want8 = np.zeros((H, W, 3), np.uint8)
+    po.port().oracle_tonemap(want.reshape(-1), W * H, 1.0, 20, want8.reshape(-1))
+    got, got8 = renderer.postprocess(bloom=True, want_sum=True, want_rgb8=True)
+    assert got.tobytes() == want.tobytes()
+    assert got8.tobytes() == want8.tobytes()
