@@ -248,26 +248,27 @@ class Renderer:
         return self
 
     @staticmethod
-    def _opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing=False, pass_group=0):
+    def _opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing=False, pass_group=0, root_start=False):
         return RenderOpts(1 if sort else 0, pass_spp, pass_first, pass_count, 1 if collect_stats else 0, stream_id, sort_bits,
-                          pass_group, 1 if timing else 0)
+                          pass_group, (1 if timing else 0) | (2 if root_start else 0))
 
     def render(self, sort=True, out=None, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0,
-               timing=False, pass_group=0):
-        """rt_render: host output (float32[H,W,3] un-normalised sums). ``out`` may be a preallocated (pinned) array."""
+               timing=False, pass_group=0, root_start=False):
+        """rt_render: host output (float32[H,W,3] un-normalised sums). ``out`` may be a preallocated (pinned) array.
+        ``root_start`` makes primary rays walk from the BVH root instead of their tile's entry records (same results)."""
         if out is None:
             out = np.empty((self.height, self.width, 3), np.float32)
         assert out.dtype == np.float32 and out.size == self.width * self.height * 3 and out.flags.c_contiguous
-        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group)
+        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group, root_start)
         st = Stats()
         _check(lib().rt_render(self._ctx, C.byref(o), out.ctypes.data, C.byref(st)), self._ctx)
         self.last_stats = st
         return out
 
     def render_device(self, sort=True, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0,
-                      timing=False, pass_group=0):
+                      timing=False, pass_group=0, root_start=False):
         """rt_render_device: returns the device pointer (int) of the float32[H*W*3] framebuffer."""
-        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group)
+        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group, root_start)
         st = Stats()
         ptr = C.c_void_p()
         _check(lib().rt_render_device(self._ctx, C.byref(o), C.byref(ptr), C.byref(st)), self._ctx)

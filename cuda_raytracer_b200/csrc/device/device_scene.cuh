@@ -29,7 +29,8 @@ constexpr int kLeafCountShift = 27;
 constexpr uint32_t kLeafStartMask = (1u << kLeafCountShift) - 1u;
 constexpr int kMaxLeafTris = 15;
 constexpr int kMaxPassGroup = 16;  // passes traced together as one wave (rt_render_opts.pass_group)
-constexpr int kStackDepth = 32;  // per-thread traversal stack entries in shared memory
+constexpr int kStackDepth = 32;  // deepest packed tree the tracer accepts
+constexpr int kStackSlots = kStackDepth + 8;  // stack entries per thread: tree depth + the entry records of a primary ray
 
 // accept t iff t > kTMin: the reference rejects `t < 0.005` in DOUBLE (scene.cu:190,357,366); 0.005f is the largest
 // float below 0.005, so for float t:  (double)t < 0.005  <=>  t <= 0.005f.
@@ -88,6 +89,8 @@ struct BounceArgs {
     unsigned long long pcg_inc;  // 820957824423429 | 1 for stream 0 (random.cuh:28)
     int32_t key_bits;
     uint32_t trace_batch, trace_refill_below, trace_node_min;  // TraceTuning
+    const uint4 *entry_lists;  // per-tile entry records for primary rays (entry_lists.cuh), nullptr = start at the root
+    int32_t entry_tiles_x;
     int32_t stack_depth;    // entries per thread of the shared-memory traversal stack (= packed BVH depth, rounded up)
 };
 

@@ -12,6 +12,7 @@
 #pragma once
 
 #include "device_scene.cuh"
+#include "entry_lists.cuh"
 #include "rng_math.cuh"
 #include "shade.cuh"
 #include "traverse.cuh"
@@ -81,6 +82,29 @@ struct QueueTraceIO {
     {
         __stcs(a.hits + i, make_float2(closest, __int_as_float(prim)));
     }
+    // Primary rays start at their tile's entry records (entry_lists.cuh): far entries go on the stack with their distance
+    // bound, the nearest becomes the current record. Everything else starts at the root.
+    template <class Stack>
+    __device__ __forceinline__ void begin(uint32_t i, Stack &stack, int &sp, uint32_t &cur) const
+    {
+        sp = 0;
+        cur = 0;
+        if (!FIRST || !use_entries) return;
+        const uint32_t g = i / a.pass_rays;
+        const uint32_t pixel = (i - g * a.pass_rays) / (uint32_t)a.rays_per_pixel;
+        const uint32_t x = pixel % (uint32_t)sc.width, y = pixel / (uint32_t)sc.width;
+        const uint4 *rec = a.entry_lists + 4 * (size_t)((y / kEntryTile) * (uint32_t)a.entry_tiles_x + x / kEntryTile);
+        const uint4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2), q3 = __ldg(rec + 3);
+        const int count = (int)q0.x;
+        if (count == 0) { cur = kDoneRef; return; }
+        const uint32_t refs[kEntryMax] = {q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+        const uint32_t dists[kEntryMax] = {q2.x, q2.y, q2.z, q2.w, q3.x, q3.y, q3.z};
+#pragma unroll
+        for (int e = kEntryMax - 1; e >= 1; e--)
+            if (e < count) { stack.push(sp, refs[e], __uint_as_float(dists[e])); sp++; }
+        cur = refs[0];
+    }
+    bool use_entries;
 };
 
 template <bool STATS>
@@ -104,7 +128,7 @@ __global__ void __launch_bounds__(kBlock, SMEM ? kBlocksPerSM : kBlocksPerSMLoca
     extern __shared__ uint32_t stack_smem[];
     const uint32_t n_in = FIRST ? a.n_first : a.pc->count[a.bounce];
     TraceCounters ctr;
-    QueueTraceIO<FIRST> io{sc, a};
+    QueueTraceIO<FIRST> io{sc, a, FIRST && !STATS && a.entry_lists != nullptr};  // the counting variant walks from the root
     if (SMEM) {
         SmemStack<kBlock> stack(stack_smem, a.stack_depth);
         trace_persistent<STATS>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below, a.trace_node_min});
@@ -249,6 +273,12 @@ struct Rays6IO {  // rt_trace_closest: rays {o, d} in, {prim, t} out
     {
         out_prim[i] = prim;
         out_t[i] = closest;
+    }
+    template <class Stack>
+    __device__ __forceinline__ void begin(uint32_t, Stack &, int &sp, uint32_t &cur) const
+    {
+        sp = 0;
+        cur = 0;
     }
 };
 

@@ -43,6 +43,10 @@ struct rt_ctx {
     bool device_packed = false;  // the records in d_nodes were written by pack_built_nodes_kernel
     float built_root[8] = {};    // the root node of a device-packed tree (box for the reorder key)
     double bvh_device_ms = 0;
+    void *d_entry = nullptr;   // per-tile entry records of the primary rays (entry_lists.cuh)
+    size_t cap_entry = 0;
+    bool entry_dirty = true;   // scene or camera changed since the records were cut
+    int entry_max = kEntryMax; // RT_ENTRY_K: entries per tile, 0 = primary rays start at the root
     double sort_device_ms = 0;
     int ray_count = 0, bounces = 0;
     float exposure = 0;
@@ -206,6 +210,7 @@ int set_image_block(rt_ctx *ctx, const rt_scene_desc *s)
     if (s->width <= 0 || s->height <= 0 || s->ray_count < 0 || s->bounces < 0 || s->bounces > kMaxBounces)
         return fail(ctx, RT_ERR_INVALID, "image block: need width,height > 0, ray_count >= 0, 0 <= bounces <= 256");
     DeviceScene &d = ctx->ds;
+    ctx->entry_dirty = true;
     d.width = s->width;
     d.height = s->height;
     copy3(d.cam, s->camera_position);
@@ -249,6 +254,7 @@ extern "C" int rt_create(rt_ctx **out, int device)
     ctx->sm_count = prop.multiProcessorCount;
     RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     if (const char *e = std::getenv("RT_STACK")) ctx->stack_mode = std::strcmp(e, "local") == 0 ? 1 : 0;
+    if (const char *e = std::getenv("RT_ENTRY_K")) ctx->entry_max = std::min((int)kEntryMax, std::max(0, std::atoi(e)));
     if (const char *e = std::getenv("RT_BATCH")) ctx->trace_batch = (uint32_t)std::min(4096, std::max(4, std::atoi(e)));
     if (const char *e = std::getenv("RT_NODEMIN")) ctx->trace_node_min = (uint32_t)std::min(33, std::max(0, std::atoi(e)));
     if (const char *e = std::getenv("RT_REFILL")) ctx->trace_refill_below = (uint32_t)std::min(33, std::max(1, std::atoi(e)));
@@ -273,7 +279,7 @@ extern "C" void rt_destroy(rt_ctx *ctx)
         release(ctx->d_keys[i]); release(ctx->d_vals[i]);
     }
     release(ctx->d_hits);
-    release(ctx->d_sort_scratch); release(ctx->d_pc); release(ctx->d_totals);
+    release(ctx->d_sort_scratch); release(ctx->d_pc); release(ctx->d_totals); release(ctx->d_entry);
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
     if (ctx->ev_stop) cudaEventDestroy(ctx->ev_stop);
@@ -616,7 +622,7 @@ int enqueue_sort(rt_ctx *ctx, const uint32_t *count_ptr, size_t bound, int bits,
 namespace {
 
 // Shared-memory bytes of the traversal stack for one CTA (0 for the local-memory variant).
-size_t stack_bytes(const rt_ctx *ctx) { return ctx->stack_mode ? 0 : (size_t)std::max(4, ctx->packed_depth) * kBlock * 8; }
+size_t stack_bytes(const rt_ctx *ctx) { return ctx->stack_mode ? 0 : (size_t)(std::max(4, ctx->packed_depth) + 8) * kBlock * 8; }
 
 template <bool FIRST>
 void launch_trace(const rt_ctx *ctx, bool stats, int grid, const BounceArgs &a)
@@ -706,6 +712,15 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     if ((rc = trace_grid_size(ctx, &grid)) != RT_OK) return rc;
     const int shade_grid_max = ctx->sm_count * 8;
 
+    // entry records of the primary rays: cut once per scene + camera, reused by every pass and frame
+    const int tiles_x = (ctx->ds.width + kEntryTile - 1) / kEntryTile, tiles_y = (ctx->ds.height + kEntryTile - 1) / kEntryTile;
+    const bool use_entries = ctx->entry_max > 0 && (opts.reserved & 2) == 0;
+    if (use_entries && ctx->entry_dirty) {
+        if ((rc = reserve(ctx, &ctx->d_entry, &ctx->cap_entry, (size_t)tiles_x * tiles_y * 64)) != RT_OK) return rc;
+        build_entry_lists_kernel<<<(tiles_x * tiles_y + 127) / 128, 128, 0, ctx->stream>>>(ctx->ds, tiles_x, tiles_y, ctx->entry_max, (uint4 *)ctx->d_entry);
+        ctx->entry_dirty = false;
+    }
+
     RT_CUDA(ctx, cudaMemsetAsync(ctx->d_fb, 0, pixels * 3 * sizeof(float), ctx->stream));
     RT_CUDA(ctx, cudaMemsetAsync(ctx->d_totals, 0, sizeof(RenderTotals), ctx->stream));
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
@@ -748,10 +763,12 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             a.pcg_inc = pcg_inc;
             a.key_bits = key_bits;
             a.hits = ctx->d_hits;
-            a.stack_depth = std::max(4, ctx->packed_depth);
+            a.stack_depth = std::max(4, ctx->packed_depth) + 8;
             a.trace_batch = ctx->trace_batch;
             a.trace_refill_below = ctx->trace_refill_below;
             a.trace_node_min = ctx->trace_node_min;
+            a.entry_lists = use_entries ? (const uint4 *)ctx->d_entry : nullptr;
+            a.entry_tiles_x = tiles_x;
             // the live count of bounce b > 0 exists only on the device: size the grids for the pass's upper bound
             const int shade_grid = (int)std::min<size_t>((size_t)shade_grid_max, ((size_t)total + kShadeBlock - 1) / kShadeBlock);
             const int t_grid = (int)std::min<size_t>((size_t)grid, ((size_t)total + kBlock - 1) / kBlock);

@@ -145,6 +145,7 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
 //
 // IO policy:  bool load(uint32_t i, float3 &o, float3 &d, float &closest, int &prim)   false = nothing to trace
 //             void store(uint32_t i, float closest, int prim)
+//             void begin(uint32_t i, Stack &stack, int &sp, uint32_t &cur)           where the walk of ray i starts
 constexpr uint32_t kDoneRef = 0xFFFFFFFFu;  // never a valid leaf ref: start would exceed the 2^27 triangle limit
 constexpr int kBatch = 192;                 // default: rays a warp claims per global atomic
 constexpr int kRefillBelow = 16;           // default: refill when fewer lanes than this still hold a ray
@@ -179,7 +180,7 @@ struct HybridStack {
     // shared-window address of smem[0][threadIdx.x], taken once: through a generic pointer the compiler re-derives the
     // window base (S2R SR_CgaCtaId + 2 integer ops) at every push and pop
     uint32_t top;
-    uint2 deep[kStackDepth - kStackTop > 0 ? kStackDepth - kStackTop : 1];
+    uint2 deep[kStackSlots - kStackTop > 0 ? kStackSlots - kStackTop : 1];
     __device__ __forceinline__ explicit HybridStack(uint2 *smem) : top((uint32_t)__cvta_generic_to_shared(smem + threadIdx.x)) {}
     __device__ __forceinline__ void push(int sp, uint32_t r, float d)
     {
@@ -246,8 +247,7 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
                 if (io.load(slot, o, d, closest, prim)) {
                     inv = f3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
                     sg = ray_signs(inv);
-                    cur = 0;  // record 0 is the root
-                    sp = 0;
+                    io.begin(slot, stack, sp, cur);  // record 0 (the root), or the tile's entry records for primary rays
                     busy = true;
                 }
             }

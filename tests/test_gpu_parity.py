@@ -189,6 +189,22 @@ def test_pass_grouping_does_not_change_the_image(renderer):
     assert np.allclose(part, ref, rtol=1e-4, atol=1e-4 * ref.mean())
 
 
+@pytest.mark.parametrize("name,w,h", [("lamp", 200, 120), ("teapot", 160, 96), ("glass_teapot", 97, 61), ("cornell_plus", 64, 64),
+                                       ("spheres", 40, 30), ("cornell", 7, 5)])
+def test_primary_entry_records_do_not_change_results(renderer, name, w, h):
+    """Primary rays start at their screen tile's entry records (entry_lists.cuh) instead of the root: same live-ray counters
+    (integer, exact), same image up to float summation order, with and without the counting variant."""
+    _setup(renderer, name, w, h, 40, 6)
+    root = renderer.render(sort=False, root_start=True)
+    n_root = renderer.last_stats.live_ray_bounces
+    fast = renderer.render(sort=False)
+    assert renderer.last_stats.live_ray_bounces == n_root
+    assert np.allclose(fast, root, rtol=1e-4, atol=1e-4 * max(root.mean(), 1e-6))
+    counted = renderer.render(sort=True, collect_stats=True)
+    assert renderer.last_stats.live_ray_bounces == n_root and renderer.last_stats.internal_visits > 0 or name == "spheres"
+    assert np.allclose(counted, root, rtol=1e-4, atol=1e-4 * max(root.mean(), 1e-6))
+
+
 def test_bounce_limit_is_reported(renderer):
     scene = load("cornell").set_image(16, 16, 1, 257, 1.0)
     with pytest.raises(rt.RtError):

@@ -20,7 +20,7 @@ print(f"{name} {w}x{h}x{spp}x{bounces}: N_int {n_int:.2f} N_tri {n_tri:.2f} byte
 print(" live per bounce (1 pass):", [int(v) for v in st.live_per_bounce[:bounces]])
 for v in variants:
     kw = dict(sort=v.startswith("sort"), sort_bits=int(v[4:]) if v.startswith("sort") else 0,
-              pass_group=int(v[5:]) if v.startswith("group") else 1)
+              pass_group=int(v[5:]) if v.startswith("group") else 1, root_start="rootstart" in sys.argv)
     best = None
     for rep in range(3):
         r.render_device(timing=True, **kw)
