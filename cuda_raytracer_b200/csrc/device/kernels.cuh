@@ -28,8 +28,8 @@ constexpr int kBlocksPerSMLocal = RT_TRACE_CTAS;  // local-memory stack variant:
 
 __device__ __forceinline__ uint32_t lanemask_lt() { return (1u << (threadIdx.x & 31)) - 1u; }
 
-// Warp-aggregated accumulation: consecutive queue positions mostly belong to the same pixel (rays_per_pixel samples
-// in a row, and compaction keeps the order), so each maximal run of equal pixels inside the warp is summed with
+// Warp-aggregated accumulation: consecutive queue positions often belong to the same pixel (rays_per_pixel samples in a
+// row at bounce 0; later the compaction keeps a pixel's survivors of one octant together), so each maximal run of equal pixels inside the warp is summed with
 // shuffles and only its first lane issues the atomics. Must be called by all 32 lanes.
 __device__ __forceinline__ void add_radiance(float *framebuffer, uint32_t pixel, float3 c);
 __device__ __forceinline__ void add_radiance_warp(float *framebuffer, uint32_t pixel, float3 c)
@@ -159,8 +159,8 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
     }
     // whole CTAs iterate together: the compaction below reserves output slots once per CTA and iteration (a single
     // per-warp atomic on one counter was 50 % of this kernel's stall samples, profiles/r1b_split_lamp1k.md)
-    __shared__ uint32_t warp_count_buf[2][kShadeBlock / 32];  // double-buffered: two barriers per iteration instead of three
     __shared__ uint32_t block_base_buf[2];
+    __shared__ uint32_t oct_count_buf[2][8 * (kShadeBlock / 32)];  // [octant][warp], double-buffered: two barriers per iteration
     uint32_t parity = 0;
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t n_round = (n_in + kShadeBlock - 1u) / kShadeBlock * kShadeBlock;
@@ -222,26 +222,33 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
             }
         }
         add_radiance_warp(a.framebuffer, pixel, radiance);
-        if (write_out) {  // next-bounce compaction: survivors keep their order inside the CTA's contiguous output range
-            uint32_t *warp_count = warp_count_buf[parity];
+        // next-bounce compaction: the CTA's survivors go to one contiguous output range, grouped by the octant of their new
+        // direction (one match.any per warp + a 64-counter scan): the next bounce's warps then hold rays of one octant from
+        // neighbouring pixels, which walk the tree in the same order (bounce-1 trace -6 %, profiles/r1h)
+        if (write_out) {
+            uint32_t *oct_count = &oct_count_buf[parity][0];  // [octant][warp]
             uint32_t &block_base = block_base_buf[parity];
             parity ^= 1u;
-            const uint32_t mask = __ballot_sync(0xffffffffu, alive);
-            if (lane == 0) warp_count[warp] = __popc(mask);
+            const uint32_t oct = alive ? ((d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u)) : 8u;
+            if (lane < 8u) oct_count[lane * (kShadeBlock / 32) + warp] = 0u;
+            __syncwarp();
+            const uint32_t mask = __match_any_sync(0xffffffffu, oct);
+            if (alive && lane == (uint32_t)(__ffs(mask) - 1)) oct_count[oct * (kShadeBlock / 32) + warp] = __popc(mask);
             __syncthreads();
-            if (threadIdx.x == 0) {
-                uint32_t total = 0;
-#pragma unroll
-                for (int w = 0; w < kShadeBlock / 32; w++) {
-                    const uint32_t c = warp_count[w];
-                    warp_count[w] = total;
-                    total += c;
+            if (warp == 0) {  // exclusive scan of the 64 counters, octant-major
+                const uint32_t v0 = oct_count[2 * lane], v1 = oct_count[2 * lane + 1];
+                uint32_t incl = v0 + v1;
+                for (int off = 1; off < 32; off <<= 1) {
+                    const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+                    if (lane >= (uint32_t)off) incl += t;
                 }
-                block_base = total ? atomicAdd(out_count, total) : 0u;
+                oct_count[2 * lane] = incl - v0 - v1;
+                oct_count[2 * lane + 1] = incl - v1;
+                if (lane == 31) block_base = incl ? atomicAdd(out_count, incl) : 0u;
             }
             __syncthreads();
             if (alive) {
-                const uint32_t pos = block_base + warp_count[warp] + __popc(mask & lanemask_lt());
+                const uint32_t pos = block_base + oct_count[oct * (kShadeBlock / 32) + warp] + __popc(mask & lanemask_lt());
                 __stcs(a.out.qa + pos, make_float4(o.x, o.y, o.z, d.x));
                 __stcs(a.out.qb + pos, make_float4(d.y, d.z, T.x, T.y));
                 __stcs(a.out.qc + pos, make_float2(T.z, __uint_as_float(id)));
