@@ -143,7 +143,10 @@ __global__ void __launch_bounds__(kBlock, SMEM ? kBlocksPerSM : kBlocksPerSMLoca
 // shade_kernel: one thread per ray of the bounce: miss -> sky radiance, hit -> emission + material scatter; radiance
 // goes to the framebuffer at once, survivors are compacted into the next queue (+ optional reorder key).
 // (cuda_process_rays raytracing.cu:83-94, Scene::process_ray scene.cu:376-487, cuda_accumulate_rays :96-107)
-constexpr int kShadeBlock = 256;
+#ifndef RT_SHADE_BLOCK
+#define RT_SHADE_BLOCK 256
+#endif
+constexpr int kShadeBlock = RT_SHADE_BLOCK;  // multiple of 128 (the octant scan gives each lane of warp 0 whole counters)
 
 template <bool FIRST>
 __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc, const BounceArgs a)
@@ -235,15 +238,19 @@ __global__ void __launch_bounds__(kShadeBlock) shade_kernel(const DeviceScene sc
             const uint32_t mask = __match_any_sync(0xffffffffu, oct);
             if (alive && lane == (uint32_t)(__ffs(mask) - 1)) oct_count[oct * (kShadeBlock / 32) + warp] = __popc(mask);
             __syncthreads();
-            if (warp == 0) {  // exclusive scan of the 64 counters, octant-major
-                const uint32_t v0 = oct_count[2 * lane], v1 = oct_count[2 * lane + 1];
-                uint32_t incl = v0 + v1;
+            if (warp == 0) {  // exclusive scan of the 8 x warps counters, octant-major: kPer consecutive counters per lane
+                constexpr int kPer = 8 * (kShadeBlock / 32) / 32;
+                uint32_t v[kPer], sum = 0;
+#pragma unroll
+                for (int k = 0; k < kPer; k++) { v[k] = oct_count[kPer * lane + k]; sum += v[k]; }
+                uint32_t incl = sum;
                 for (int off = 1; off < 32; off <<= 1) {
                     const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
                     if (lane >= (uint32_t)off) incl += t;
                 }
-                oct_count[2 * lane] = incl - v0 - v1;
-                oct_count[2 * lane + 1] = incl - v1;
+                uint32_t run = incl - sum;
+#pragma unroll
+                for (int k = 0; k < kPer; k++) { oct_count[kPer * lane + k] = run; run += v[k]; }
                 if (lane == 31) block_base = incl ? atomicAdd(out_count, incl) : 0u;
             }
             __syncthreads();

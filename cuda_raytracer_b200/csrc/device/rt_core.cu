@@ -710,7 +710,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
 
     int grid = 0;
     if ((rc = trace_grid_size(ctx, &grid)) != RT_OK) return rc;
-    const int shade_grid_max = ctx->sm_count * 8;
+    const int shade_grid_max = ctx->sm_count * (2048 / kShadeBlock);
 
     // entry records of the primary rays: cut once per scene + camera, reused by every pass and frame
     const int tiles_x = (ctx->ds.width + kEntryTile - 1) / kEntryTile, tiles_y = (ctx->ds.height + kEntryTile - 1) / kEntryTile;
