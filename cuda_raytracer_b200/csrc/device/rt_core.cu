@@ -26,6 +26,9 @@ struct rt_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;  // second pipe of the pass loop: every other wave runs here (render_impl)
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    int pipes = 2;                   // RT_PIPES=1: one wave at a time
     std::string error;
 
     // scene
@@ -253,6 +256,10 @@ extern "C" int rt_create(rt_ctx **out, int device)
     RT_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
     RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
+    RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+    RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+    if (const char *e = std::getenv("RT_PIPES")) ctx->pipes = std::min(2, std::max(1, std::atoi(e)));
     if (const char *e = std::getenv("RT_STACK")) ctx->stack_mode = std::strcmp(e, "local") == 0 ? 1 : 0;
     if (const char *e = std::getenv("RT_ENTRY_K")) ctx->entry_max = std::min((int)kEntryMax, std::max(0, std::atoi(e)));
     if (const char *e = std::getenv("RT_BATCH")) ctx->trace_batch = (uint32_t)std::min(4096, std::max(4, std::atoi(e)));
@@ -260,7 +267,7 @@ extern "C" int rt_create(rt_ctx **out, int device)
     if (const char *e = std::getenv("RT_REFILL")) ctx->trace_refill_below = (uint32_t)std::min(33, std::max(1, std::atoi(e)));
     RT_CUDA(ctx, cudaEventCreate(&ctx->ev_start));
     RT_CUDA(ctx, cudaEventCreate(&ctx->ev_stop));
-    RT_CUDA(ctx, cudaMalloc(&ctx->d_pc, sizeof(PassCounters)));
+    RT_CUDA(ctx, cudaMalloc(&ctx->d_pc, 2 * sizeof(PassCounters)));  // one per pipe
     RT_CUDA(ctx, cudaMalloc(&ctx->d_totals, sizeof(RenderTotals)));
     *out = ctx;
     return RT_OK;
@@ -271,6 +278,7 @@ extern "C" void rt_destroy(rt_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->stream2) cudaStreamSynchronize(ctx->stream2);
     release(ctx->d_nodes); release(ctx->d_tris); release(ctx->d_materials); release(ctx->d_spheres); release(ctx->d_env);
     release(ctx->d_matidx); release(ctx->d_raw); release(ctx->d_build); if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     release(ctx->d_fb); release(ctx->d_fb_tmp); release(ctx->d_fb_tmp2); release(ctx->d_rgb8);
@@ -283,6 +291,9 @@ extern "C" void rt_destroy(rt_ctx *ctx)
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
     if (ctx->ev_stop) cudaEventDestroy(ctx->ev_stop);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -625,15 +636,15 @@ namespace {
 size_t stack_bytes(const rt_ctx *ctx) { return ctx->stack_mode ? 0 : (size_t)(std::max(4, ctx->packed_depth) + 8) * kBlock * 8; }
 
 template <bool FIRST>
-void launch_trace(const rt_ctx *ctx, bool stats, int grid, const BounceArgs &a)
+void launch_trace(const rt_ctx *ctx, cudaStream_t stream, bool stats, int grid, const BounceArgs &a)
 {
     const size_t smem = stack_bytes(ctx);
     if (ctx->stack_mode) {
-        if (stats) trace_rays_kernel<FIRST, true, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->ds, a);
-        else trace_rays_kernel<FIRST, false, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->ds, a);
+        if (stats) trace_rays_kernel<FIRST, true, false><<<grid, kBlock, 0, stream>>>(ctx->ds, a);
+        else trace_rays_kernel<FIRST, false, false><<<grid, kBlock, 0, stream>>>(ctx->ds, a);
     } else {
-        if (stats) trace_rays_kernel<FIRST, true, true><<<grid, kBlock, smem, ctx->stream>>>(ctx->ds, a);
-        else trace_rays_kernel<FIRST, false, true><<<grid, kBlock, smem, ctx->stream>>>(ctx->ds, a);
+        if (stats) trace_rays_kernel<FIRST, true, true><<<grid, kBlock, smem, stream>>>(ctx->ds, a);
+        else trace_rays_kernel<FIRST, false, true><<<grid, kBlock, smem, stream>>>(ctx->ds, a);
     }
 }
 
@@ -668,6 +679,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     std::vector<int> ev_kind;                       // 0 = trace kernel, 1 = reorder, 2 = shade kernel
     std::vector<int> ev_bounce;
     int cur_bounce = 0;
+    cudaStream_t cur_stream = ctx->stream;  // the pipe the wave in hand runs on
     auto mark = [&](int kind) -> int {
         if (!timing) return RT_OK;
         size_t k = ev_kind.size();
@@ -678,7 +690,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         }
         ev_kind.push_back(kind);
         ev_bounce.push_back(cur_bounce);
-        return cudaEventRecord(ctx->ev_pool[k], ctx->stream) == cudaSuccess ? RT_OK : RT_ERR_CUDA;
+        return cudaEventRecord(ctx->ev_pool[k], cur_stream) == cudaSuccess ? RT_OK : RT_ERR_CUDA;
     };
     const bool sort = opts.sort != 0 && ctx->bounces > 1;
     int key_bits = opts.sort_bits > 0 ? opts.sort_bits : 15;  // 4 bits per axis + octant = two 8-bit digit passes
@@ -701,12 +713,25 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     }
     max_group = std::max(1, std::min({max_group, (int)kMaxPassGroup, pass_end - pass_first}));
     while (max_group > 1 && pass_rays_max * (size_t)max_group >= (1ull << 31)) max_group--;
+    // Two PIPES: consecutive waves alternate between two streams, each with its own half of the queues and its own
+    // counters. A wave is a chain of dependent launches whose late bounces hold a few 10^4 rays and whose persistent
+    // tracer drains warp by warp at the end of every launch; with a second, independent wave in flight those SMs pick up
+    // its CTAs instead of idling, and the HBM-latency-bound shade kernel of one wave overlaps the issue-bound tracer of the
+    // other. The automatic wave size is halved so that the memory in use stays the same. Not with the reorder pass (its
+    // scratch is single), not with per-kernel event timing or counting (their numbers are per kernel, alone on the GPU).
+    int pipes = (sort || timing || collect || (opts.reserved & 4) || pass_end - pass_first < 2) ? 1 : ctx->pipes;
+    if (pipes > 1 && opts.pass_group <= 0) max_group = std::max(1, std::min(max_group / 2, (pass_end - pass_first + 1) / 2));
     // the automatic wave size is a guess at what the allocator will grant: on an out-of-memory answer try smaller waves
-    while ((rc = ensure_queues(ctx, pass_rays_max * (size_t)max_group, sort)) == RT_ERR_NOMEM && opts.pass_group <= 0 && max_group > 1) {
+    for (;;) {
+        rc = ensure_queues(ctx, pass_rays_max * (size_t)max_group * (size_t)pipes, sort);
+        if (rc != RT_ERR_NOMEM) break;
         cudaGetLastError();
-        max_group = (max_group + 1) / 2;
+        if (opts.pass_group <= 0 && max_group > 1) max_group = (max_group + 1) / 2;
+        else if (pipes > 1) pipes = 1;  // an explicit wave size that fits once but not twice
+        else break;
     }
     if (rc != RT_OK) return rc;
+    const size_t pipe_stride = pass_rays_max * (size_t)max_group;  // queue positions per pipe
 
     int grid = 0;
     if ((rc = trace_grid_size(ctx, &grid)) != RT_OK) return rc;
@@ -724,8 +749,12 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     RT_CUDA(ctx, cudaMemsetAsync(ctx->d_fb, 0, pixels * 3 * sizeof(float), ctx->stream));
     RT_CUDA(ctx, cudaMemsetAsync(ctx->d_totals, 0, sizeof(RenderTotals), ctx->stream));
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
+    if (pipes > 1) {
+        RT_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
+        RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
+    }
 
-    int launches = 0, passes_done = 0;
+    int launches = 0, passes_done = 0, wave = 0;
     long long primaries = 0;
     // A WAVE is `group` consecutive passes of equal size traced together: every pass keeps the reference's seeds
     // (they depend on the pass, not on the launch), while the late bounces - a few 10^4 rays per pass, latency-bound -
@@ -740,16 +769,21 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         for (int g = 0; g < group; g++) remaining[g] = ctx->ray_count - (pass + g) * pass_spp - rays_to_cast;
         const uint32_t total = pass_rays * (uint32_t)group;
         primaries += total;
-        RT_CUDA(ctx, cudaMemsetAsync(ctx->d_pc, 0, sizeof(PassCounters), ctx->stream));
+        const int pipe = wave++ % pipes;
+        cur_stream = pipe ? ctx->stream2 : ctx->stream;
+        PassCounters *pc = ctx->d_pc + pipe;
+        const size_t qoff = (size_t)pipe * pipe_stride;
+        auto pipe_queue = [&](int i) { return RayQueue{ctx->queue[i].qa + qoff, ctx->queue[i].qb + qoff, ctx->queue[i].qc + qoff}; };
+        RT_CUDA(ctx, cudaMemsetAsync(pc, 0, sizeof(PassCounters), cur_stream));
         const uint32_t *order = nullptr;
         for (int b = 0; b < ctx->bounces; b++) {
             BounceArgs a{};
             cur_bounce = b;
-            a.in = ctx->queue[(b + 1) & 1];
-            a.out = (b + 1 < ctx->bounces) ? ctx->queue[b & 1] : RayQueue{nullptr, nullptr, nullptr};
+            a.in = pipe_queue((b + 1) & 1);
+            a.out = (b + 1 < ctx->bounces) ? pipe_queue(b & 1) : RayQueue{nullptr, nullptr, nullptr};
             a.order = order;
             a.keys_out = (sort && b + 1 < ctx->bounces) ? ctx->d_keys[0] : nullptr;
-            a.pc = ctx->d_pc;
+            a.pc = pc;
             a.totals = ctx->d_totals;
             a.framebuffer = ctx->d_fb;
             a.n_first = total;
@@ -762,7 +796,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             }
             a.pcg_inc = pcg_inc;
             a.key_bits = key_bits;
-            a.hits = ctx->d_hits;
+            a.hits = ctx->d_hits + qoff;
             a.stack_depth = std::max(4, ctx->packed_depth) + 8;
             a.trace_batch = ctx->trace_batch;
             a.trace_refill_below = ctx->trace_refill_below;
@@ -773,12 +807,12 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             const int shade_grid = (int)std::min<size_t>((size_t)shade_grid_max, ((size_t)total + kShadeBlock - 1) / kShadeBlock);
             const int t_grid = (int)std::min<size_t>((size_t)grid, ((size_t)total + kBlock - 1) / kBlock);
             if ((rc = mark(0)) != RT_OK) return fail(ctx, rc, "event record failed");
-            if (b == 0) launch_trace<true>(ctx, collect, t_grid, a);
-            else launch_trace<false>(ctx, collect, t_grid, a);
+            if (b == 0) launch_trace<true>(ctx, cur_stream, collect, t_grid, a);
+            else launch_trace<false>(ctx, cur_stream, collect, t_grid, a);
             if ((rc = mark(0)) != RT_OK) return fail(ctx, rc, "event record failed");
             if ((rc = mark(2)) != RT_OK) return fail(ctx, rc, "event record failed");
-            if (b == 0) shade_kernel<true><<<shade_grid, kShadeBlock, 0, ctx->stream>>>(ctx->ds, a);
-            else shade_kernel<false><<<shade_grid, kShadeBlock, 0, ctx->stream>>>(ctx->ds, a);
+            if (b == 0) shade_kernel<true><<<shade_grid, kShadeBlock, 0, cur_stream>>>(ctx->ds, a);
+            else shade_kernel<false><<<shade_grid, kShadeBlock, 0, cur_stream>>>(ctx->ds, a);
             if ((rc = mark(2)) != RT_OK) return fail(ctx, rc, "event record failed");
             launches += 2;
             order = nullptr;
@@ -792,6 +826,10 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         }
         passes_done += group;
         pass += group;
+    }
+    if (pipes > 1) {
+        RT_CUDA(ctx, cudaEventRecord(ctx->ev_join, ctx->stream2));
+        RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
     }
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
     RT_CUDA(ctx, cudaGetLastError());

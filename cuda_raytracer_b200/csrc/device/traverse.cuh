@@ -28,19 +28,66 @@ struct TraceCounters {
 // direction picks ahead of time (rounding is monotonic, so (lo-o)*inv <= (hi-o)*inv whenever inv >= 0). fmaxf/fminf
 // drop a NaN operand exactly as the reference's chain does, and the three-operand forms compile to FMNMX3.
 // Arithmetic per bound is (bound - o) * inv as the reference writes it; there is no a*b+c shape to contract.
+// RT_SIGN_MASK (default 1): the signs are kept as all-ones / all-zeros words and the near / far bound of an axis is a
+// bitwise select (one LOP3 each, same count as the FSELs) — predicates would have to be rebuilt from registers at every
+// visited record (3 LOP3 per visit) because they do not survive the loop.
+#ifndef RT_SIGN_MASK
+#define RT_SIGN_MASK 1
+#endif
+#if RT_SIGN_MASK
+struct RaySigns {
+    uint32_t x, y, z;  // 0xFFFFFFFF when the direction component is negative (including -0: 1/-0 = -inf), else 0
+};
+__device__ __forceinline__ RaySigns ray_signs(float3 inv)
+{
+    return RaySigns{(uint32_t)(__float_as_int(inv.x) >> 31), (uint32_t)(__float_as_int(inv.y) >> 31), (uint32_t)(__float_as_int(inv.z) >> 31)};
+}
+__device__ __forceinline__ float pick(uint32_t m, float a, float b)  // m ? a : b
+{
+    return __uint_as_float((__float_as_uint(a) & m) | (__float_as_uint(b) & ~m));
+}
+#else
 struct RaySigns {
     bool x, y, z;  // direction component negative (including -0: 1/-0 = -inf)
 };
 __device__ __forceinline__ RaySigns ray_signs(float3 inv) { return RaySigns{signbit(inv.x) != 0, signbit(inv.y) != 0, signbit(inv.z) != 0}; }
+__device__ __forceinline__ float pick(bool m, float a, float b) { return m ? a : b; }
+#endif
 
-__device__ __forceinline__ bool slab(float lox, float loy, float loz, float hix, float hiy, float hiz, float3 o, float3 inv,
+// RT_SLAB_FMA (default 1): t of a bound is taken as fma(bound, inv, -(o * inv)) instead of (bound - o) * inv: one FFMA
+// instead of FADD + FMUL per bound (12 instructions fewer per visited record). The two forms differ by rounding only
+// (absolute error ~ulp(o * inv) instead of a relative one), near and far t of a flat box are still computed identically,
+// and for an axis-parallel ray (inv = +-inf) the FMA form yields NaN = "no constraint on this axis" where the exact
+// form yields +-inf: the walk then visits a superset of the records, and hits come from the exact triangle test.
+// `so` is what slab_origin() returned for the ray.
+#ifndef RT_SLAB_FMA
+#define RT_SLAB_FMA 1
+#endif
+__device__ __forceinline__ float3 slab_origin(float3 o, float3 inv)
+{
+#if RT_SLAB_FMA
+    return f3(-(o.x * inv.x), -(o.y * inv.y), -(o.z * inv.z));
+#else
+    (void)inv;
+    return o;
+#endif
+}
+__device__ __forceinline__ float slab_t(float bound, float so, float inv)
+{
+#if RT_SLAB_FMA
+    return __fmaf_rn(bound, inv, so);
+#else
+    return (bound - so) * inv;
+#endif
+}
+__device__ __forceinline__ bool slab(float lox, float loy, float loz, float hix, float hiy, float hiz, float3 so, float3 inv,
                                      RaySigns sg, float limit, float &t_enter)
 {
-    const float nx = sg.x ? hix : lox, fx = sg.x ? lox : hix;
-    const float ny = sg.y ? hiy : loy, fy = sg.y ? loy : hiy;
-    const float nz = sg.z ? hiz : loz, fz = sg.z ? loz : hiz;
-    const float tn = fmaxf(fmaxf((nx - o.x) * inv.x, (ny - o.y) * inv.y), fmaxf((nz - o.z) * inv.z, 0.0f));
-    const float tf = fminf(fminf((fx - o.x) * inv.x, (fy - o.y) * inv.y), fminf((fz - o.z) * inv.z, limit));
+    const float nx = pick(sg.x, hix, lox), fx = pick(sg.x, lox, hix);
+    const float ny = pick(sg.y, hiy, loy), fy = pick(sg.y, loy, hiy);
+    const float nz = pick(sg.z, hiz, loz), fz = pick(sg.z, loz, hiz);
+    const float tn = fmaxf(fmaxf(slab_t(nx, so.x, inv.x), slab_t(ny, so.y, inv.y)), fmaxf(slab_t(nz, so.z, inv.z), 0.0f));
+    const float tf = fminf(fminf(slab_t(fx, so.x, inv.x), slab_t(fy, so.y, inv.y)), fminf(slab_t(fz, so.z, inv.z), limit));
     t_enter = tn;
     return tn <= tf;
 }
@@ -63,6 +110,24 @@ __device__ __forceinline__ void intersect_spheres(const DeviceScene &sc, float3 
     }
 }
 
+// RT_FAST_RCP (default 1): 1 / a of the triangle test through MUFU.RCP alone (rcp.approx, <= 1 ulp, subnormal inputs
+// handled) instead of the IEEE division sequence (range check + 3 fix-up instructions + a slow-path call): u, v and t
+// move by at most an ulp, far inside the 1e-5 relative bar on t; the reference's own GPU build divides with
+// --use_fast_math.
+#ifndef RT_FAST_RCP
+#define RT_FAST_RCP 1
+#endif
+__device__ __forceinline__ float tri_rcp(float a)
+{
+#if RT_FAST_RCP
+    float r;
+    asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(a));
+    return r;
+#else
+    return 1.0f / a;
+#endif
+}
+
 // Moller-Trumbore on the precomputed-edge record (scene.cu:164-194). Updates closest/prim on an accepted hit.
 __device__ __forceinline__ void intersect_triangle(const float4 *__restrict__ tris, uint32_t tri, int prim_base, float3 o, float3 d,
                                                    float &closest, int &prim)
@@ -74,7 +139,7 @@ __device__ __forceinline__ void intersect_triangle(const float4 *__restrict__ tr
     float3 h = cross(d, e2);
     float a = dot(h, e1);
     if (a == 0.0f) return;
-    float inv_a = 1.0f / a;
+    float inv_a = tri_rcp(a);
     float3 s = o - p1;
     float u = dot(s, h) * inv_a;
     if (u < 0.0f || u > 1.0f) return;
@@ -93,6 +158,7 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
 {
     const float3 inv = f3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     const RaySigns sg = ray_signs(inv);
+    const float3 so = slab_origin(o, inv);
     const float4 *__restrict__ nodes = sc.nodes;
     const int lane = threadIdx.x;
     uint32_t cur = 0;  // record 0 is the root
@@ -104,8 +170,8 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
             const uint2 q3 = make_uint2(__float_as_uint(na.hi.z), __float_as_uint(nb.hi.z));
             if (STATS) ctr.internal_visits++;
             float d0, d1;
-            bool h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, o, inv, sg, closest, d0);
-            bool h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, o, inv, sg, closest, d1);
+            bool h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, so, inv, sg, closest, d0);
+            bool h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, so, inv, sg, closest, d1);
             if (h0 && h1) {
                 bool zero_near = d0 < d1;
                 uint32_t far_ref = zero_near ? q3.y : q3.x;
@@ -150,6 +216,9 @@ constexpr uint32_t kDoneRef = 0xFFFFFFFFu;  // never a valid leaf ref: start wou
 constexpr int kBatch = 192;                 // default: rays a warp claims per global atomic
 constexpr int kRefillBelow = 16;           // default: refill when fewer lanes than this still hold a ray
 constexpr int kNodeMin = 12;                // default for TraceTuning::node_min
+#ifndef RT_TUNE_RUNTIME
+#define RT_TUNE_RUNTIME 0
+#endif
 struct TraceTuning {
     uint32_t batch;         // rays per claim; the kernel shrinks it when the bounce has fewer rays than batch x warps
     uint32_t refill_below;
@@ -214,16 +283,20 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
     // instead of queueing `batch` rays behind a few warps.
     const uint32_t warps = gridDim.x * (blockDim.x >> 5);
     const uint32_t batch = max(4u, min(tune.batch, (n + warps - 1) / warps));
+#if RT_TUNE_RUNTIME  // sweeps: thresholds from RT_REFILL / RT_NODEMIN (one LDCU per visited record)
     const uint32_t refill_below = tune.refill_below;
     const uint32_t node_min = tune.node_min;
+#else
+    constexpr uint32_t refill_below = kRefillBelow, node_min = kNodeMin;
+#endif
     uint32_t pool_next = 0, pool_end = 0;  // warp-uniform: unclaimed part of the current batch
     bool exhausted = false;                // warp-uniform: the global cursor ran past n
     bool busy = false;
     uint32_t slot = 0, cur = kDoneRef;
     int sp = 0, prim = -1;
     float closest = kMissT;
-    float3 o = f3(0, 0, 0), d = f3(0, 0, 1), inv = f3(0, 0, 1);
-    RaySigns sg{false, false, false};
+    float3 o = f3(0, 0, 0), d = f3(0, 0, 1), inv = f3(0, 0, 1), so = f3(0, 0, 0);
+    RaySigns sg = ray_signs(inv);
 
     for (;;) {
         // ---- refill: all 32 lanes are here ----
@@ -247,6 +320,7 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
                 if (io.load(slot, o, d, closest, prim)) {
                     inv = f3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
                     sg = ray_signs(inv);
+                    so = slab_origin(o, inv);
                     io.begin(slot, stack, sp, cur);  // record 0 (the root), or the tile's entry records for primary rays
                     busy = true;
                 }
@@ -274,8 +348,8 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
                 const uint2 q3 = make_uint2(__float_as_uint(na.hi.z), __float_as_uint(nb.hi.z));
                 if (STATS) ctr.internal_visits++;
                 float d0, d1;
-                const bool h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, o, inv, sg, closest, d0);
-                const bool h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, o, inv, sg, closest, d1);
+                const bool h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, so, inv, sg, closest, d0);
+                const bool h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, so, inv, sg, closest, d1);
                 if (h0 && h1) {
                     const bool zero_near = d0 < d1;
                     stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
