@@ -189,6 +189,28 @@ def test_pass_grouping_does_not_change_the_image(renderer):
     assert np.allclose(part, ref, rtol=1e-4, atol=1e-4 * ref.mean())
 
 
+def test_two_pipes_equal_one_pipe(monkeypatch):
+    """Consecutive waves alternate between two streams (render_impl's pipes) with their own queue halves and counters:
+    same counters (integer, exact) and the same image up to float summation order as one wave at a time, for an odd and
+    an even number of waves, a ragged last pass, explicit and automatic wave sizes."""
+    imgs, counts = {}, {}
+    for pipes in ("1", "2"):
+        monkeypatch.setenv("RT_PIPES", pipes)
+        r = rt.Renderer(0)
+        try:
+            r.upload(load("cornell_plus").set_image(56, 40, 130, 7, 1.0))  # 7 passes: 6 x 20 + 10
+            for group in (0, 1, 2, 3):
+                imgs[pipes, group] = r.render(sort=False, pass_group=group)
+                st = r.last_stats
+                counts[pipes, group] = (st.live_ray_bounces, st.primary_rays, st.passes, tuple(st.live_per_bounce[:7]))
+        finally:
+            r.close()
+    ref = imgs["1", 1]
+    for key, img in imgs.items():
+        assert counts[key] == counts["1", 1], key
+        assert np.allclose(img, ref, rtol=1e-4, atol=1e-4 * ref.mean()), key
+
+
 @pytest.mark.parametrize("name,w,h", [("lamp", 200, 120), ("teapot", 160, 96), ("glass_teapot", 97, 61), ("cornell_plus", 64, 64),
                                        ("spheres", 40, 30), ("cornell", 7, 5)])
 def test_primary_entry_records_do_not_change_results(renderer, name, w, h):
