@@ -19,6 +19,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "device_scene.cuh"  // RT_BOX_CH: the record layout pack_built_nodes_kernel writes
+
 namespace rtd {
 
 constexpr int kBuildBlock = 256;     // one CTA per node: the many small nodes of the lower levels
@@ -394,8 +396,19 @@ __global__ void pack_built_nodes_kernel(const BuildNode *__restrict__ nodes, int
             if (count > max_leaf || count <= 0) { *needs_host = 1; return; }
             ref = leaf_bit | ((uint32_t)count << count_shift) | (uint32_t)ch.child2;
         }
+#if RT_BOX_CH  // centre + half-extent rounded up (same arithmetic as the host packer's set_box, rt_core.cu)
+        float cc[3], hh[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            cc[k] = __fadd_rn(__fmul_rn(0.5f, ch.lo[k]), __fmul_rn(0.5f, ch.hi[k]));
+            hh[k] = fmaxf(__fsub_ru(ch.hi[k], cc[k]), __fsub_ru(cc[k], ch.lo[k]));
+        }
+        rec[2 * c] = make_float4(cc[0], cc[1], cc[2], hh[0]);
+        rec[2 * c + 1] = make_float4(hh[1], hh[2], __uint_as_float(ref), 0.0f);
+#else
         rec[2 * c] = make_float4(ch.lo[0], ch.lo[1], ch.lo[2], ch.hi[0]);
         rec[2 * c + 1] = make_float4(ch.hi[1], ch.hi[2], __uint_as_float(ref), 0.0f);
+#endif
     }
 }
 

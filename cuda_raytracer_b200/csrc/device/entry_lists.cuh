@@ -89,7 +89,12 @@ __global__ void build_entry_lists_kernel(const DeviceScene sc, int tiles_x, int 
         for (int e = 0; e < count; e++) {
             const float4 *nd = sc.nodes + 4 * (size_t)ref[e];
             const float4 a0 = __ldg(nd), a1 = __ldg(nd + 1), b0 = __ldg(nd + 2), b1 = __ldg(nd + 3);
+#if RT_BOX_CH  // {centre, half-extent} -> bounds, rounded outwards
+            const float lo0[3] = {__fsub_rd(a0.x, a0.w), __fsub_rd(a0.y, a1.x), __fsub_rd(a0.z, a1.y)}, hi0[3] = {__fadd_ru(a0.x, a0.w), __fadd_ru(a0.y, a1.x), __fadd_ru(a0.z, a1.y)};
+            const float lo1[3] = {__fsub_rd(b0.x, b0.w), __fsub_rd(b0.y, b1.x), __fsub_rd(b0.z, b1.y)}, hi1[3] = {__fadd_ru(b0.x, b0.w), __fadd_ru(b0.y, b1.x), __fadd_ru(b0.z, b1.y)};
+#else
             const float lo0[3] = {a0.x, a0.y, a0.z}, hi0[3] = {a0.w, a1.x, a1.y}, lo1[3] = {b0.x, b0.y, b0.z}, hi1[3] = {b0.w, b1.x, b1.y};
+#endif
             const uint32_t r0 = __float_as_uint(a1.z), r1 = __float_as_uint(b1.z);
             // an empty child has its box parked far away; treat it as absent
             const bool t0 = r0 != kEmptyRef && frustum_may_touch(f, lo0, hi0), t1 = r1 != kEmptyRef && frustum_may_touch(f, lo1, hi1);

@@ -4,6 +4,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -26,9 +27,12 @@ struct rt_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
-    cudaStream_t stream2 = nullptr;  // second pipe of the pass loop: every other wave runs here (render_impl)
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+    static constexpr int kMaxPipes = 4;
+    cudaStream_t side[kMaxPipes - 1] = {};  // further pipes of the pass loop: wave w runs on pipe w % pipes (render_impl)
+    cudaEvent_t ev_fork = nullptr, ev_join[kMaxPipes - 1] = {};
     int pipes = 2;                   // RT_PIPES=1: one wave at a time
+    int trace_per_sm = 0;            // RT_TRACE_PER_SM: CTAs per SM of the persistent tracer grid (0 = full occupancy)
+    int shade_per_sm = 0;            // RT_SHADE_PER_SM: CTAs per SM of the shade grid (0 = 2048 threads' worth)
     std::string error;
 
     // scene
@@ -123,8 +127,19 @@ struct Packer {
     static void set_box(PackedRecord &r, int child, const float *lo, const float *hi)
     {
         float *b = r.child[child].box;
+#if RT_BOX_CH  // centre + half-extent rounded up: differences of floats are exact in double, so this is __fsub_ru
+        for (int k = 0; k < 3; k++) {
+            const float c = 0.5f * lo[k] + 0.5f * hi[k];
+            const double hd = std::max((double)hi[k] - (double)c, (double)c - (double)lo[k]);
+            float h = (float)hd;
+            if ((double)h < hd) h = std::nextafterf(h, INFINITY);
+            b[k] = c;
+            b[3 + k] = h;
+        }
+#else
         b[0] = lo[0]; b[1] = lo[1]; b[2] = lo[2];
         b[3] = hi[0]; b[4] = hi[1]; b[5] = hi[2];
+#endif
     }
     static void set_empty(PackedRecord &r, int child)
     {
@@ -256,10 +271,14 @@ extern "C" int rt_create(rt_ctx **out, int device)
     RT_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
     RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-    RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->stream2, cudaStreamNonBlocking));
     RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
-    RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
-    if (const char *e = std::getenv("RT_PIPES")) ctx->pipes = std::min(2, std::max(1, std::atoi(e)));
+    for (int i = 0; i < rt_ctx::kMaxPipes - 1; i++) {
+        RT_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->side[i], cudaStreamNonBlocking));
+        RT_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join[i], cudaEventDisableTiming));
+    }
+    if (const char *e = std::getenv("RT_PIPES")) ctx->pipes = std::min((int)rt_ctx::kMaxPipes, std::max(1, std::atoi(e)));
+    if (const char *e = std::getenv("RT_TRACE_PER_SM")) ctx->trace_per_sm = std::max(0, std::atoi(e));
+    if (const char *e = std::getenv("RT_SHADE_PER_SM")) ctx->shade_per_sm = std::max(0, std::atoi(e));
     if (const char *e = std::getenv("RT_STACK")) ctx->stack_mode = std::strcmp(e, "local") == 0 ? 1 : 0;
     if (const char *e = std::getenv("RT_ENTRY_K")) ctx->entry_max = std::min((int)kEntryMax, std::max(0, std::atoi(e)));
     if (const char *e = std::getenv("RT_BATCH")) ctx->trace_batch = (uint32_t)std::min(4096, std::max(4, std::atoi(e)));
@@ -267,7 +286,7 @@ extern "C" int rt_create(rt_ctx **out, int device)
     if (const char *e = std::getenv("RT_REFILL")) ctx->trace_refill_below = (uint32_t)std::min(33, std::max(1, std::atoi(e)));
     RT_CUDA(ctx, cudaEventCreate(&ctx->ev_start));
     RT_CUDA(ctx, cudaEventCreate(&ctx->ev_stop));
-    RT_CUDA(ctx, cudaMalloc(&ctx->d_pc, 2 * sizeof(PassCounters)));  // one per pipe
+    RT_CUDA(ctx, cudaMalloc(&ctx->d_pc, rt_ctx::kMaxPipes * sizeof(PassCounters)));  // one per pipe
     RT_CUDA(ctx, cudaMalloc(&ctx->d_totals, sizeof(RenderTotals)));
     *out = ctx;
     return RT_OK;
@@ -278,7 +297,7 @@ extern "C" void rt_destroy(rt_ctx *ctx)
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    if (ctx->stream2) cudaStreamSynchronize(ctx->stream2);
+    for (cudaStream_t s : ctx->side) if (s) cudaStreamSynchronize(s);
     release(ctx->d_nodes); release(ctx->d_tris); release(ctx->d_materials); release(ctx->d_spheres); release(ctx->d_env);
     release(ctx->d_matidx); release(ctx->d_raw); release(ctx->d_build); if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     release(ctx->d_fb); release(ctx->d_fb_tmp); release(ctx->d_fb_tmp2); release(ctx->d_rgb8);
@@ -292,8 +311,8 @@ extern "C" void rt_destroy(rt_ctx *ctx)
     if (ctx->ev_start) cudaEventDestroy(ctx->ev_start);
     if (ctx->ev_stop) cudaEventDestroy(ctx->ev_stop);
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
-    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
-    if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
+    for (cudaEvent_t e : ctx->ev_join) if (e) cudaEventDestroy(e);
+    for (cudaStream_t s : ctx->side) if (s) cudaStreamDestroy(s);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -656,6 +675,7 @@ int trace_grid_size(rt_ctx *ctx, int *out)
         RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_rays_kernel<false, false, false>, kBlock, 0));
     else
         RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_rays_kernel<false, false, true>, kBlock, stack_bytes(ctx)));
+    if (ctx->trace_per_sm > 0) per_sm = std::min(per_sm, ctx->trace_per_sm);
     *out = ctx->sm_count * std::max(1, per_sm);
     return RT_OK;
 }
@@ -713,21 +733,22 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     }
     max_group = std::max(1, std::min({max_group, (int)kMaxPassGroup, pass_end - pass_first}));
     while (max_group > 1 && pass_rays_max * (size_t)max_group >= (1ull << 31)) max_group--;
-    // Two PIPES: consecutive waves alternate between two streams, each with its own half of the queues and its own
+    // PIPES (2 by default, RT_PIPES=1..4): consecutive waves rotate over that many streams, each with its own share of the queues and its own
     // counters. A wave is a chain of dependent launches whose late bounces hold a few 10^4 rays and whose persistent
     // tracer drains warp by warp at the end of every launch; with a second, independent wave in flight those SMs pick up
     // its CTAs instead of idling, and the HBM-latency-bound shade kernel of one wave overlaps the issue-bound tracer of the
-    // other. The automatic wave size is halved so that the memory in use stays the same. Not with the reorder pass (its
+    // other. The automatic wave size is divided by the pipes so that the memory in use stays the same. Not with the reorder pass (its
     // scratch is single), not with per-kernel event timing or counting (their numbers are per kernel, alone on the GPU).
     int pipes = (sort || timing || collect || (opts.reserved & 4) || pass_end - pass_first < 2) ? 1 : ctx->pipes;
-    if (pipes > 1 && opts.pass_group <= 0) max_group = std::max(1, std::min(max_group / 2, (pass_end - pass_first + 1) / 2));
+    pipes = std::min(pipes, pass_end - pass_first);
+    if (pipes > 1 && opts.pass_group <= 0) max_group = std::max(1, std::min(max_group / pipes, (pass_end - pass_first + pipes - 1) / pipes));
     // the automatic wave size is a guess at what the allocator will grant: on an out-of-memory answer try smaller waves
     for (;;) {
         rc = ensure_queues(ctx, pass_rays_max * (size_t)max_group * (size_t)pipes, sort);
         if (rc != RT_ERR_NOMEM) break;
         cudaGetLastError();
         if (opts.pass_group <= 0 && max_group > 1) max_group = (max_group + 1) / 2;
-        else if (pipes > 1) pipes = 1;  // an explicit wave size that fits once but not twice
+        else if (pipes > 1) pipes--;  // an explicit wave size that fits once but not `pipes` times
         else break;
     }
     if (rc != RT_OK) return rc;
@@ -735,7 +756,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
 
     int grid = 0;
     if ((rc = trace_grid_size(ctx, &grid)) != RT_OK) return rc;
-    const int shade_grid_max = ctx->sm_count * (2048 / kShadeBlock);
+    const int shade_grid_max = ctx->sm_count * (ctx->shade_per_sm > 0 ? ctx->shade_per_sm : 2048 / kShadeBlock);
 
     // entry records of the primary rays: cut once per scene + camera, reused by every pass and frame
     const int tiles_x = (ctx->ds.width + kEntryTile - 1) / kEntryTile, tiles_y = (ctx->ds.height + kEntryTile - 1) / kEntryTile;
@@ -751,7 +772,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
     if (pipes > 1) {
         RT_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
-        RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->ev_fork, 0));
+        for (int i = 0; i < pipes - 1; i++) RT_CUDA(ctx, cudaStreamWaitEvent(ctx->side[i], ctx->ev_fork, 0));
     }
 
     int launches = 0, passes_done = 0, wave = 0;
@@ -770,7 +791,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         const uint32_t total = pass_rays * (uint32_t)group;
         primaries += total;
         const int pipe = wave++ % pipes;
-        cur_stream = pipe ? ctx->stream2 : ctx->stream;
+        cur_stream = pipe ? ctx->side[pipe - 1] : ctx->stream;
         PassCounters *pc = ctx->d_pc + pipe;
         const size_t qoff = (size_t)pipe * pipe_stride;
         auto pipe_queue = [&](int i) { return RayQueue{ctx->queue[i].qa + qoff, ctx->queue[i].qb + qoff, ctx->queue[i].qc + qoff}; };
@@ -828,8 +849,10 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         pass += group;
     }
     if (pipes > 1) {
-        RT_CUDA(ctx, cudaEventRecord(ctx->ev_join, ctx->stream2));
-        RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+        for (int i = 0; i < pipes - 1; i++) {
+            RT_CUDA(ctx, cudaEventRecord(ctx->ev_join[i], ctx->side[i]));
+            RT_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join[i], 0));
+        }
     }
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
     RT_CUDA(ctx, cudaGetLastError());

@@ -34,7 +34,12 @@ struct TraceCounters {
 #ifndef RT_SIGN_MASK
 #define RT_SIGN_MASK 1
 #endif
-#if RT_SIGN_MASK
+#if RT_BOX_CH
+struct RaySigns {
+    float x, y, z;  // |1 / d|: the centre / half-extent form needs no signs
+};
+__device__ __forceinline__ RaySigns ray_signs(float3 inv) { return RaySigns{fabsf(inv.x), fabsf(inv.y), fabsf(inv.z)}; }
+#elif RT_SIGN_MASK
 struct RaySigns {
     uint32_t x, y, z;  // 0xFFFFFFFF when the direction component is negative (including -0: 1/-0 = -inf), else 0
 };
@@ -63,6 +68,9 @@ __device__ __forceinline__ float pick(bool m, float a, float b) { return m ? a :
 #ifndef RT_SLAB_FMA
 #define RT_SLAB_FMA 1
 #endif
+#if RT_BOX_CH && !RT_SLAB_FMA
+#error "RT_BOX_CH needs RT_SLAB_FMA"
+#endif
 __device__ __forceinline__ float3 slab_origin(float3 o, float3 inv)
 {
 #if RT_SLAB_FMA
@@ -80,6 +88,19 @@ __device__ __forceinline__ float slab_t(float bound, float so, float inv)
     return (bound - so) * inv;
 #endif
 }
+#if RT_BOX_CH
+// the six floats are {centre.xyz, half-extent.xyz}; a flat box (h = 0) gives t_near == t_far exactly, an axis-parallel ray
+// (inv = +-inf) gives NaN on that axis = no constraint (a superset of the exact form's visits, as with RT_SLAB_FMA)
+__device__ __forceinline__ bool slab(float cx, float cy, float cz, float hx, float hy, float hz, float3 so, float3 inv,
+                                     RaySigns ainv, float limit, float &t_enter)
+{
+    const float tx = __fmaf_rn(cx, inv.x, so.x), ty = __fmaf_rn(cy, inv.y, so.y), tz = __fmaf_rn(cz, inv.z, so.z);
+    const float tn = fmaxf(fmaxf(__fmaf_rn(-hx, ainv.x, tx), __fmaf_rn(-hy, ainv.y, ty)), fmaxf(__fmaf_rn(-hz, ainv.z, tz), 0.0f));
+    const float tf = fminf(fminf(__fmaf_rn(hx, ainv.x, tx), __fmaf_rn(hy, ainv.y, ty)), fminf(__fmaf_rn(hz, ainv.z, tz), limit));
+    t_enter = tn;
+    return tn <= tf;
+}
+#else
 __device__ __forceinline__ bool slab(float lox, float loy, float loz, float hix, float hiy, float hiz, float3 so, float3 inv,
                                      RaySigns sg, float limit, float &t_enter)
 {
@@ -91,6 +112,7 @@ __device__ __forceinline__ bool slab(float lox, float loy, float loz, float hix,
     t_enter = tn;
     return tn <= tf;
 }
+#endif
 
 // scene.cu:338-372. Returns through closest/prim; runs before the BVH and seeds `closest`.
 __device__ __forceinline__ void intersect_spheres(const DeviceScene &sc, float3 o, float3 d, float &closest, int &prim)
