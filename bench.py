@@ -380,7 +380,7 @@ def main():
     # bytes per live ray-bounce x the ray-bounces one average launch of the timed region processed
     traffic = None
     try:
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r1h_traffic.json")))
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r1k_traffic.json")))
         n_trace_launches = max(1, sum(p[2] for p in attr_step) // 2)  # every bounce = one trace + one shade launch (sort off)
         traffic = tr["dram_bytes_per_live_ray_bounce"] * sum(p[1] for p in attr_step) / n_trace_launches
     except (OSError, KeyError, ValueError):
@@ -402,7 +402,7 @@ def main():
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "traffic_note": "DRAM bytes per average trace launch, from profiles/r1h_traffic.json (ncu --set full); algorithmic bytes per such launch = achieved x its duration: the BVH bytes are L1/L2 hits",
+                     "traffic_note": "DRAM bytes per average trace launch, from profiles/r1k_traffic.json (ncu --set full); algorithmic bytes per such launch = achieved x its duration: the BVH bytes are L1/L2 hits",
                      "kernel": "trace_rays_kernel", "bytes_per_ray_bounce": trace_bytes_per_unit, "n_int": n_int, "n_tri": n_tri,
                      "whole_bounce_bytes_per_ray_bounce": bytes_per_unit,
                      "whole_step_achieved": sum(p[1] for p in per_step) * bytes_per_unit / max(1e-9, sum(p[0] for p in per_step)) * 1e-9,
