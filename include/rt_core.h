@@ -80,8 +80,10 @@ typedef struct rt_render_opts {
                               that do NOT want pass-identical images */
     int32_t sort_bits;     /* key width for the reorder pass, 0 = default */
     int32_t pass_group;    /* passes traced together as one wave: 0 = auto (memory budget, at most 16), 1 = one pass per wave as the
-                              reference does. Results do not depend on it beyond float summation order. */
+                              reference does. Results do not depend on it beyond float summation order. With sort = 0 two
+                              waves are in flight at a time on two streams of the context (environment RT_PIPES=1: one). */
     int32_t reserved;      /* bit 0: time every bounce kernel / reorder pass with CUDA events (rt_stats.trace_ms, shade_ms, sort_ms);
+                            *        one wave at a time, so that every interval is one kernel's own;
                             * bit 1: primary rays walk from the BVH root instead of their screen tile's entry records (same results) */
 } rt_render_opts;
 
