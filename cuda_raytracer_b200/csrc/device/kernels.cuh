@@ -148,11 +148,15 @@ __global__ void __launch_bounds__(kBlock, SMEM ? kBlocksPerSM : kBlocksPerSMLoca
 #endif
 constexpr int kShadeBlock = RT_SHADE_BLOCK;  // multiple of 128 (the octant scan gives each lane of warp 0 whole counters)
 
-#ifndef RT_SHADE_MIN_CTAS
-#define RT_SHADE_MIN_CTAS 1
+// RT_SHADE_MIN_CTAS (A/B): minimum CTAs per SM given to __launch_bounds__, i.e. a register cap; without it ptxas settles on
+// 47 (first bounce) / 63 registers = 5 / 4 CTAs per SM
+#ifdef RT_SHADE_MIN_CTAS
+#define RT_SHADE_BOUNDS __launch_bounds__(kShadeBlock, RT_SHADE_MIN_CTAS)
+#else
+#define RT_SHADE_BOUNDS __launch_bounds__(kShadeBlock)
 #endif
 template <bool FIRST>
-__global__ void __launch_bounds__(kShadeBlock, RT_SHADE_MIN_CTAS) shade_kernel(const DeviceScene sc, const BounceArgs a)
+__global__ void RT_SHADE_BOUNDS shade_kernel(const DeviceScene sc, const BounceArgs a)
 {
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n_in = FIRST ? a.n_first : a.pc->count[a.bounce];
