@@ -46,6 +46,28 @@ constexpr int kStackSlots = kStackDepth + 8;  // stack entries per thread: tree 
 constexpr float kTMin = 0.005f;
 constexpr float kMissT = 1e30f;
 
+// Division of a 32-bit index by a launch-invariant divisor (rays per pass, samples per pixel, image width) without the
+// ~20-instruction software division: Granlund & Montgomery's multiply-and-shift, exact for every 32-bit numerator.
+// m = floor(2^32 (2^L - d) / d) + 1 with L = ceil(log2 d);  n / d = (((n - hi(m n)) >> min(L, 1)) + hi(m n)) >> max(L - 1, 0).
+struct FastDiv {
+    uint32_t m, sh1, sh2, d;
+};
+inline FastDiv make_fast_div(uint32_t d)
+{
+    if (d == 0) d = 1;
+    uint32_t L = 0;
+    while (L < 32 && (1ull << L) < d) L++;
+    const uint64_t m = ((1ull << 32) * ((1ull << L) - d)) / d + 1;
+    return FastDiv{(uint32_t)m, L < 1 ? L : 1u, L > 1 ? L - 1 : 0u, d};
+}
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t fast_div(uint32_t n, const FastDiv &f)
+{
+    const uint32_t q = __umulhi(f.m, n);
+    return (((n - q) >> f.sh1) + q) >> f.sh2;
+}
+#endif
+
 struct DeviceScene {
     const float4 *nodes;      // 4 per internal record
     const float4 *tris;       // 4 per triangle (64-byte records)
@@ -55,6 +77,7 @@ struct DeviceScene {
     const uint16_t *material_indices;
     int32_t sphere_count, tri_count, env_w, env_h;
     int32_t width, height;
+    FastDiv div_width;
     float cam[3], top_left[3], right[3], up[3];
     float inv_width, inv_height;
     float min_coord[3], inv_dim[3];          // the reference's key bounds (scene.cu:822-830), kept for completeness
@@ -93,6 +116,7 @@ struct BounceArgs {
     uint32_t pass_rays;     // rays of ONE pass (pixels x rays_per_pixel); ray id = pass-in-wave x pass_rays + index in pass
     int32_t bounce;
     int32_t rays_per_pixel; // of every pass of this wave
+    FastDiv div_pass_rays, div_rays_per_pixel;
     uint32_t gen_seed[kMaxPassGroup];   // per pass of the wave: 709579 * remaining_rays           (scene.cu:81)
     uint32_t proc_seed[kMaxPassGroup];  // per pass of the wave: 279220567 * (remaining*20+bounce)  (raytracing.cu:89,236)
     unsigned long long pcg_inc;  // 820957824423429 | 1 for stream 0 (random.cuh:28)

@@ -67,8 +67,8 @@ struct QueueTraceIO {
     __device__ __forceinline__ bool load(uint32_t i, float3 &o, float3 &d, float &closest, int &prim) const
     {
         if (FIRST) {
-            const uint32_t g = i / a.pass_rays;  // pass of the wave; seeds and pixel follow the index inside that pass
-            if (!generate_ray(sc, i - g * a.pass_rays, a.rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d)) return false;
+            const uint32_t g = fast_div(i, a.div_pass_rays);  // pass of the wave; seeds and pixel follow the index inside that pass
+            if (!generate_ray(sc, i - g * a.pass_rays, a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d)) return false;
         } else {
             const uint32_t slot = a.order ? __ldg(a.order + i) : i;
             const float4 ra = __ldcs(a.in.qa + slot), rb = __ldcs(a.in.qb + slot);
@@ -90,9 +90,9 @@ struct QueueTraceIO {
         sp = 0;
         cur = 0;
         if (!FIRST || !use_entries) return;
-        const uint32_t g = i / a.pass_rays;
-        const uint32_t pixel = (i - g * a.pass_rays) / (uint32_t)a.rays_per_pixel;
-        const uint32_t x = pixel % (uint32_t)sc.width, y = pixel / (uint32_t)sc.width;
+        const uint32_t g = fast_div(i, a.div_pass_rays);
+        const uint32_t pixel = fast_div(i - g * a.pass_rays, a.div_rays_per_pixel);
+        const uint32_t y = fast_div(pixel, sc.div_width), x = pixel - y * (uint32_t)sc.width;
         const uint4 *rec = a.entry_lists + 4 * (size_t)((y / kEntryTile) * (uint32_t)a.entry_tiles_x + x / kEntryTile);
         const uint4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2), q3 = __ldg(rec + 3);
         const int count = (int)q0.x;
@@ -205,8 +205,8 @@ __global__ void RT_SHADE_BOUNDS shade_kernel(const DeviceScene sc, const BounceA
         uint32_t id = i;
         if (active) {
             if (FIRST) {
-                const uint32_t g = id / a.pass_rays;
-                active = generate_ray(sc, id - g * a.pass_rays, a.rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d);
+                const uint32_t g = fast_div(id, a.div_pass_rays);
+                active = generate_ray(sc, id - g * a.pass_rays, a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d);
             } else {
                 o = f3(cur.ra.x, cur.ra.y, cur.ra.z);
                 d = f3(cur.ra.w, cur.rb.x, cur.rb.y);
@@ -221,8 +221,8 @@ __global__ void RT_SHADE_BOUNDS shade_kernel(const DeviceScene sc, const BounceA
             const float2 h = cur.h;
             const float closest = h.x;
             const int prim = __float_as_int(h.y);
-            const uint32_t g = id / a.pass_rays, index = id - g * a.pass_rays;  // pass of the wave, ray index inside it
-            pixel = index / (uint32_t)a.rays_per_pixel;
+            const uint32_t g = fast_div(id, a.div_pass_rays), index = id - g * a.pass_rays;  // pass of the wave, ray index inside it
+            pixel = fast_div(index, a.div_rays_per_pixel);
             if (prim < 0) {
                 radiance = shade_miss(sc, d) * T;
             } else {
@@ -324,7 +324,7 @@ __global__ void __launch_bounds__(kBlock, SMEM ? kBlocksPerSM : kBlocksPerSMLoca
 }
 
 // 12 floats per ray: origin, direction, transmitted = 1, collected = 0 (RayData, scene.cuh:61-68)
-__global__ void generate_kernel(const DeviceScene sc, int rays_per_pixel, uint32_t first, uint32_t n, uint32_t gen_seed,
+__global__ void generate_kernel(const DeviceScene sc, FastDiv rays_per_pixel, uint32_t first, uint32_t n, uint32_t gen_seed,
                                 unsigned long long inc, float *__restrict__ out12)
 {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;

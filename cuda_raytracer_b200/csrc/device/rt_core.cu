@@ -230,6 +230,7 @@ int set_image_block(rt_ctx *ctx, const rt_scene_desc *s)
     DeviceScene &d = ctx->ds;
     ctx->entry_dirty = true;
     d.width = s->width;
+    d.div_width = make_fast_div((uint32_t)std::max(1, s->width));
     d.height = s->height;
     copy3(d.cam, s->camera_position);
     copy3(d.top_left, s->near_plane_top_left);
@@ -811,6 +812,8 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             a.pass_rays = pass_rays;
             a.bounce = b;
             a.rays_per_pixel = rays_to_cast;
+            a.div_pass_rays = make_fast_div(pass_rays);
+            a.div_rays_per_pixel = make_fast_div((uint32_t)rays_to_cast);
             for (int g = 0; g < group; g++) {
                 a.gen_seed[g] = 709579u * (uint32_t)remaining[g];                      // scene.cu:81
                 a.proc_seed[g] = 279220567u * (uint32_t)(remaining[g] * 20 + b);       // raytracing.cu:89,236
@@ -1018,7 +1021,7 @@ extern "C" int rt_generate_rays(rt_ctx *ctx, int32_t rays_per_pixel, int32_t fir
     DeviceBuffer out;
     RT_CUDA(ctx, cudaMalloc(&out.p, (size_t)n * 12 * sizeof(float)));
     RT_CUDA(ctx, cudaMemsetAsync(out.p, 0, (size_t)n * 12 * sizeof(float), ctx->stream));
-    generate_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->ds, rays_per_pixel, (uint32_t)first, (uint32_t)n, 709579u * (uint32_t)seed,
+    generate_kernel<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->ds, make_fast_div((uint32_t)rays_per_pixel), (uint32_t)first, (uint32_t)n, 709579u * (uint32_t)seed,
                                                               820957824423429ULL | 1ULL, (float *)out.p);
     RT_CUDA(ctx, cudaGetLastError());
     RT_CUDA(ctx, cudaMemcpyAsync(out12, out.p, (size_t)n * 12 * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));

@@ -11,12 +11,12 @@ namespace rtd {
 
 // Primary ray `ray_index` of a pass of `rays_per_pixel` samples. Contraction is forbidden so that the direction is
 // bit-identical to the host oracle (the whole bounce-0 hit comparison rests on identical rays).
-__device__ __forceinline__ bool generate_ray(const DeviceScene &sc, uint32_t ray_index, int rays_per_pixel, uint32_t gen_seed_term,
+__device__ __forceinline__ bool generate_ray(const DeviceScene &sc, uint32_t ray_index, const FastDiv &rays_per_pixel, uint32_t gen_seed_term,
                                              unsigned long long inc, float3 &o, float3 &d)
 {
     Pcg rng = pcg_seed(ray_index * 2239826922u + gen_seed_term, inc);  // 298592570346 mod 2^32 = 2239826922 (scene.cu:81)
-    uint32_t pixel = ray_index / (uint32_t)rays_per_pixel;
-    uint32_t x = pixel % (uint32_t)sc.width, y = pixel / (uint32_t)sc.width;
+    const uint32_t pixel = fast_div(ray_index, rays_per_pixel);
+    const uint32_t y = fast_div(pixel, sc.div_width), x = pixel - y * (uint32_t)sc.width;
     if (y >= (uint32_t)sc.height) return false;
     float xs = __fmul_rn(__fadd_rn((float)x, rnd01(rng)), sc.inv_width);
     float ys = __fmul_rn(__fadd_rn((float)y, rnd01(rng)), sc.inv_height);
