@@ -73,7 +73,7 @@ EXPORTS = [
     # rt_core.h
     "rt_api_version", "rt_device_count", "rt_create", "rt_destroy", "rt_last_error", "rt_scene_upload", "rt_scene_set_image",
     "rt_render", "rt_render_device", "rt_postprocess", "rt_framebuffer_upload", "rt_trace_closest", "rt_generate_rays",
-    "rt_process_rays", "rt_sort_pairs", "rt_scene_download_bvh", "rt_scene_bvh_device_ms", "rt_sort_device_ms",
+    "rt_process_rays", "rt_sort_pairs", "rt_scene_download_bvh", "rt_scene_bvh_device_ms", "rt_sort_device_ms", "rt_index_divide",
     # rt_scene.h
     "rt_scene_load", "rt_scene_free", "rt_scene_describe", "rt_scene_set_image_host", "rt_scene_camera_raw",
     "rt_scene_bvh_build_ms", "rt_write_png",
@@ -112,6 +112,8 @@ def lib():
     L.rt_scene_bvh_device_ms.restype = C.c_double
     L.rt_sort_device_ms.argtypes = [vp]
     L.rt_sort_device_ms.restype = C.c_double
+    L.rt_index_divide.argtypes = [C.c_uint32, C.c_uint32]
+    L.rt_index_divide.restype = C.c_uint32
     L.rt_scene_load.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(vp)]
     L.rt_scene_free.argtypes = [vp]
     L.rt_scene_free.restype = None

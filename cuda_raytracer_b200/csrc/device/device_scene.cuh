@@ -61,9 +61,13 @@ inline FastDiv make_fast_div(uint32_t d)
     return FastDiv{(uint32_t)m, L < 1 ? L : 1u, L > 1 ? L - 1 : 0u, d};
 }
 #ifdef __CUDACC__
-__device__ __forceinline__ uint32_t fast_div(uint32_t n, const FastDiv &f)
+__host__ __device__ __forceinline__ uint32_t fast_div(uint32_t n, const FastDiv &f)
 {
+#ifdef __CUDA_ARCH__
     const uint32_t q = __umulhi(f.m, n);
+#else
+    const uint32_t q = (uint32_t)(((uint64_t)f.m * n) >> 32);  // host mirror, reachable through rt_index_divide (tests)
+#endif
     return (((n - q) >> f.sh1) + q) >> f.sh2;
 }
 #endif

@@ -1093,6 +1093,8 @@ extern "C" int rt_sort_pairs(rt_ctx *ctx, uint32_t *keys, uint32_t *values, int3
 }
 extern "C" double rt_sort_device_ms(const rt_ctx *ctx) { return ctx ? ctx->sort_device_ms : 0.0; }
 
+extern "C" uint32_t rt_index_divide(uint32_t n, uint32_t d) { return rtd::fast_div(n, rtd::make_fast_div(d)); }
+
 // ---- device BVH build: inspection hooks ---------------------------------------------------------------------------
 extern "C" double rt_scene_bvh_device_ms(const rt_ctx *ctx) { return ctx ? ctx->bvh_device_ms : 0.0; }
 

@@ -159,6 +159,9 @@ int rt_process_rays(rt_ctx *ctx, float *ray_data12, const uint32_t *seeds, int32
 int rt_sort_pairs(rt_ctx *ctx, uint32_t *keys, uint32_t *values, int32_t n, int32_t bits);
 /* CUDA-event time of the sort kernels of the last rt_sort_pairs call (copies excluded), in milliseconds. */
 double rt_sort_device_ms(const rt_ctx *ctx);
+/* Host mirror of the kernels' index arithmetic (ray id -> pass / pixel / row: n / d by multiply-and-shift with the constants
+ * the render call derives from d). Needs no device; d = 0 is treated as 1. Test hook. */
+uint32_t rt_index_divide(uint32_t n, uint32_t d);
 
 #ifdef __cplusplus
 }

@@ -100,3 +100,21 @@ def test_front_end_usage_and_exit_codes(tmp_path):
     assert r.returncode == 1 and "sage" in (r.stdout + r.stderr)
     r = subprocess.run([exe, "cornell.scene", "no_gpu"], cwd=SCENES, capture_output=True, text=True)
     assert r.returncode == 2 and "No raytracing hardware specified" in (r.stdout + r.stderr)
+
+
+def test_index_division_by_multiply_and_shift_is_exact():
+    """The kernels map a ray id to its pass, pixel and row with n / d computed as multiply-high + two shifts (FastDiv,
+    device_scene.cuh); rt_index_divide runs the same constants and formula on the host. Exact for every 32-bit numerator:
+    the divisors the render call uses (samples per pixel, widths, rays per pass up to 2^31), powers of two and their
+    neighbours, and random pairs, each at the numerators where a wrong constant shows first (multiples of d and +-1)."""
+    import random
+    lib = rt.lib()
+    rng = random.Random(5)
+    divisors = [1, 2, 3, 5, 7, 20, 21, 33, 64, 97, 1000, 1920, 3840, 165_888_000, 2**31 - 1, 2**31, 2**31 + 1, 2**32 - 1]
+    divisors += [2**k + o for k in range(1, 32) for o in (-1, 0, 1) if 2**k + o > 0] + [rng.randrange(1, 2**32) for _ in range(200)]
+    for d in divisors:
+        ns = {0, 1, d - 1, d, d + 1, 2**32 - 1, 2**32 - 2, 2**31, (2**32 - 1) // d * d, max(0, (2**32 - 1) // d * d - 1)}
+        ns |= {rng.randrange(0, 2**32) for _ in range(40)} | {min(2**32 - 1, k * d + o) for k in (2, 3, 1000) for o in (-1, 0)}
+        for n in (n for n in ns if 0 <= n < 2**32):
+            assert lib.rt_index_divide(n, d) == n // d, (n, d)
+    assert lib.rt_index_divide(12345, 0) == 12345  # d = 0 is treated as 1
