@@ -35,7 +35,10 @@ float Box::half_area() const
 
 namespace {
 
-constexpr int kBins = 8;
+#ifndef RT_HOST_BINS
+#define RT_HOST_BINS 8  // the reference's bin count (scene.cu:866-1000); other values only for tree-quality experiments
+#endif
+constexpr int kBins = RT_HOST_BINS;
 
 struct SplitPlane {
     int axis = -1;
