@@ -235,7 +235,7 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
 //             void store(uint32_t i, float closest, int prim)
 //             void begin(uint32_t i, Stack &stack, int &sp, uint32_t &cur)           where the walk of ray i starts
 constexpr uint32_t kDoneRef = 0xFFFFFFFFu;  // never a valid leaf ref: start would exceed the 2^27 triangle limit
-constexpr int kBatch = 192;                 // default: rays a warp claims per global atomic
+constexpr int kBatch = 512;                 // default: rays a warp claims per global atomic (re-swept in r1m: 192 -> 512 = +0.6-1 %)
 constexpr int kRefillBelow = 16;           // default: refill when fewer lanes than this still hold a ray
 constexpr int kNodeMin = 12;                // default for TraceTuning::node_min
 #ifndef RT_TUNE_RUNTIME
