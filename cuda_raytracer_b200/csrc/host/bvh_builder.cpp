@@ -39,6 +39,9 @@ namespace {
 #define RT_HOST_BINS 8  // the reference's bin count (scene.cu:866-1000); other values only for tree-quality experiments
 #endif
 constexpr int kBins = RT_HOST_BINS;
+#ifndef RT_HOST_LEAF
+#define RT_HOST_LEAF 4  // the reference stops splitting at <= 4 triangles (scene.cu:880)
+#endif
 
 struct SplitPlane {
     int axis = -1;
@@ -113,7 +116,7 @@ struct Builder {
         nodes[node_index].box = box;
 
         int count = end - begin;
-        if (count <= 4 || depth_left == 0) return;
+        if (count <= RT_HOST_LEAF || depth_left == 0) return;
 
         float leaf_cost = box.half_area() * count;
         SplitPlane plane = best_plane(scene.triangles, begin, end, leaf_cost);
