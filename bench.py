@@ -421,6 +421,23 @@ def main():
         line["bvh_build_ms"] = {"host_binned_sah": scene.bvh_build_ms, "device_binned_sah": r.bvh_device_ms,
                                 "triangles": int(a.triangle_count), "nodes": int(a.bvh_node_count)}
         r.upload(scene)
+    if world == 1:  # the same workload on the host tree WITH spatial splits (rt_scene_load(use_bvh = 3)): not the headline, whose
+        # tree is the reference's own; same hits and image, fewer visited records (profiles/r1m_sbvh.md)
+        t0 = time.perf_counter()
+        sb_scene = rt.load_scene(scene_name + ".scene", use_bvh="sbvh", cwd=SCENES).set_image(w, h, spp, bounces)
+        sb_load_s = time.perf_counter() - t0
+        r.upload(sb_scene)
+        r.render_device(sort=sort, pass_first=first, pass_count=count, pass_group=args.pass_group)  # warm-up
+        sb_s, sb_live = 0.0, 0
+        for _ in range(args.steps):
+            r.render_device(sort=sort, pass_first=first, pass_count=count, pass_group=args.pass_group)
+            sb_s += r.last_stats.loop_seconds
+            sb_live += r.last_stats.live_ray_bounces
+        line["sbvh_tree"] = {"value": sb_live / max(sb_s, 1e-9) * 1e-6, "unit": "Mrays/s", "ms_per_step": sb_s / args.steps * 1e3,
+                             "triangle_references": int(sb_scene.desc().triangle_count), "triangles": int(a.triangle_count),
+                             "nodes": int(sb_scene.desc().bvh_node_count), "load_and_build_ms": sb_load_s * 1e3,
+                             "note": "rt_scene_load(use_bvh = 3): host tree with spatial splits instead of the reference's tree; same core, same image"}
+        r.upload(scene)
     if world == 1 and not args.no_cpu_baseline and os.path.exists(REF_BIN):
         ratio, threads = live_per_primary(scene_name, w, h, bounces)
         s_spp = size_cpu_sample(scene_name, w, h, bounces, 12.0)

@@ -144,9 +144,12 @@ class Scene:
     """A host scene (rt_host_scene): what the reference's ``load_scene`` fills into its ``Scene`` struct."""
 
     def __init__(self, path, use_bvh=True, verbose=False, cwd=None):
-        """use_bvh: True / False as the reference's flag; "device" (= 2) defers the BVH build to the GPU."""
+        """use_bvh: True / False as the reference's flag; "device" (= 2) defers the BVH build to the GPU; "sbvh" (= 3) builds
+        a spatial-split tree on the host (same hits, fewer visited records; not the reference's tree)."""
         if use_bvh == "device":
             use_bvh = 2
+        elif use_bvh == "sbvh":
+            use_bvh = 3
         self._h = C.c_void_p()
         old = os.getcwd()
         if cwd:

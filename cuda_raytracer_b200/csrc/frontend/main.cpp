@@ -2,7 +2,7 @@
 // (/root/reference/raytracing.cu:305-398): same argument grammar, exit codes (1 usage / CUDA error, 2 no hardware),
 // stdout lines and ./raytracing.png output. The render itself goes through the C ABI (rt_core.h); there is no CPU
 // renderer in this product, so `cpu` without a GPU path is refused with exit code 2 like "no hardware".
-// Extra words the reference would ignore: out=<path>, stats, no_bloom, device=<n>, gpu_bvh (build the BVH on the device).
+// Extra words the reference would ignore: out=<path>, stats, no_bloom, device=<n>, gpu_bvh (build the BVH on the device), sbvh (host tree with spatial splits).
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -18,7 +18,7 @@ int main(int argc, char **argv)
         std::printf("Usage: %s <scene>\n", argv[0]);
         return 1;
     }
-    bool sort = true, cpu = false, gpu = true, bvh = true, bloom = true, stats_on = false, gpu_bvh = false;
+    bool sort = true, cpu = false, gpu = true, bvh = true, bloom = true, stats_on = false, gpu_bvh = false, sbvh = false;
     int device = 0;
     std::string out_path = "raytracing.png";
     for (int i = 2; i < argc; i++) {
@@ -30,6 +30,7 @@ int main(int argc, char **argv)
         else if (!std::strcmp(w, "no_bloom")) bloom = false;
         else if (!std::strcmp(w, "stats")) stats_on = true;
         else if (!std::strcmp(w, "gpu_bvh")) gpu_bvh = true;
+        else if (!std::strcmp(w, "sbvh")) sbvh = true;
         else if (!std::strncmp(w, "out=", 4)) out_path = w + 4;
         else if (!std::strncmp(w, "device=", 7)) device = std::atoi(w + 7);
     }
@@ -40,7 +41,7 @@ int main(int argc, char **argv)
     if (cpu) std::printf("note: `cpu` ignored, this build renders on the GPU only\n");
 
     rt_host_scene *scene = nullptr;
-    if (rt_scene_load(argv[1], bvh ? (gpu_bvh ? 2 : 1) : 0, 1, &scene) != RT_OK) {
+    if (rt_scene_load(argv[1], bvh ? (gpu_bvh ? 2 : (sbvh ? 3 : 1)) : 0, 1, &scene) != RT_OK) {
         std::printf("Error loading scene: %s\n", rt_last_error(nullptr));
         return 1;
     }

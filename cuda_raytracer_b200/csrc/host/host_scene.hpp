@@ -87,7 +87,7 @@ struct HostScene {
     int triangles_form = 0;  // 1 = build form, file order: the BVH is built by the render core on the device
 
     void precompute_camera();
-    void build_tree(int max_depth, bool verbose);  // bvh_builder.cpp
+    void build_tree(int max_depth, bool verbose, bool spatial_splits = false);  // bvh_builder.cpp
     void defer_tree(bool verbose);                 // bvh_builder.cpp: root node only, triangles stay in build form
     void compute_bounds();
 };
@@ -98,6 +98,6 @@ struct LoadError {
 };
 
 // Throws LoadError. scene_loader.cpp
-void load_scene_file(HostScene &scene, const char *path, int use_bvh, bool verbose);  // 0 no_bvh, 1 host build, 2 deferred
+void load_scene_file(HostScene &scene, const char *path, int use_bvh, bool verbose);  // 0 no_bvh, 1 host build, 2 deferred, 3 host build with spatial splits
 
 }  // namespace rt

@@ -25,7 +25,7 @@ int rt_scene_load(const char *path, int use_bvh, int verbose, rt_host_scene **ou
     rt_host_scene *h = new (std::nothrow) rt_host_scene();
     if (!h) return RT_ERR_NOMEM;
     try {
-        rt::load_scene_file(h->scene, path, use_bvh < 0 ? 0 : (use_bvh > 2 ? 1 : use_bvh), verbose != 0);
+        rt::load_scene_file(h->scene, path, use_bvh < 0 ? 0 : (use_bvh > 3 ? 1 : use_bvh), verbose != 0);
     } catch (const rt::LoadError &e) {
         rt::set_global_error(e.message);
         delete h;

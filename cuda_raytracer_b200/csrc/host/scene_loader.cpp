@@ -308,7 +308,7 @@ void load_scene_file(HostScene &scene, const char *path, int use_bvh, bool verbo
     }
     scene.precompute_camera();
     if (use_bvh == 2) scene.defer_tree(verbose);
-    else scene.build_tree(use_bvh ? 30 : 0, verbose);  // MAX_BVH_DEPTH, scene.cu:10,820
+    else scene.build_tree(use_bvh ? 30 : 0, verbose, use_bvh == 3);  // MAX_BVH_DEPTH, scene.cu:10,820
     scene.compute_bounds();
 }
 

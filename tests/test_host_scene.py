@@ -216,3 +216,31 @@ def test_png_writer_roundtrip(tmp_path):
     raw = np.frombuffer(zlib.decompress(idat), np.uint8).reshape(37, 1 + 53 * 3)
     assert (raw[:, 0] == 0).all()  # filter type 0 on every row
     assert (raw[:, 1:].reshape(37, 53, 3) == img).all()
+
+
+@pytest.mark.parametrize("name", ["cornell_plus", "teapot"])
+def test_spatial_split_tree_gives_the_same_hits(name, monkeypatch):
+    """use_bvh="sbvh" (rt_scene_load(use_bvh = 3)) selects the spatial-split builder (bvh_builder.cpp; not the reference's tree):
+    triangles that straddle a split plane are referenced from both children. Whatever the tree, closest hits must not
+    change: same hit / miss per ray and the same t as on the reference's tree (walked by the oracle), arrays consistent
+    (every leaf range inside the triangle array, materials carried along with the repeated triangles)."""
+    from util import oracle_arrays, oracle_closest, scene_rays
+    monkeypatch.delenv("RT_SBVH", raising=False)
+    ref = rt.load_scene(name + ".scene", cwd=SCENES).set_image(64, 48, 20, 6, 1.0)
+    A0 = oracle_arrays(ref)
+    sb = rt.load_scene(name + ".scene", use_bvh="sbvh", cwd=SCENES).set_image(64, 48, 20, 6, 1.0)
+    A1 = oracle_arrays(sb)
+    assert len(A1.triangles) >= len(A0.triangles) and len(A1.material_indices) == len(A1.spheres) + len(A1.triangles)
+    leaves = A1.bvh[A1.bvh["child2"] <= A1.bvh["child1"]] if A1.bvh.dtype.names and "child1" in A1.bvh.dtype.names else None
+    if leaves is not None:
+        assert (leaves["child2"] >= 0).all() and (leaves["child1"] <= len(A1.triangles)).all()
+    rays = scene_rays(A0, 30_000, seed=13)
+    p0, t0, c0 = oracle_closest(A0, rays, 1)
+    p1, t1, c1 = oracle_closest(A1, rays, 1)
+    assert ((p0 >= 0) == (p1 >= 0)).all()
+    hit = p0 >= 0
+    assert np.allclose(t0[hit], t1[hit], rtol=1e-6, atol=0)
+    ns = len(A0.spheres)
+    tri = hit & (p0 >= ns)
+    same_material = A0.material_indices[p0[tri]] == A1.material_indices[p1[tri]]
+    assert same_material.mean() > 0.999  # a different triangle only on exact-t ties between neighbours
