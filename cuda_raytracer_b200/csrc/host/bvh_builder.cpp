@@ -219,6 +219,7 @@ struct SpatialBuilder {
     float root_area = 0;
     size_t ref_budget = 0;               // stop splitting in space once this many references exist
     size_t ref_total = 0;
+    float alpha = 1e-5f;                 // spatial splits are tried where the object split's children overlap by more than alpha x root area
     long spatial_splits = 0, object_splits = 0;
 
     struct Choice {
@@ -341,7 +342,7 @@ struct SpatialBuilder {
         bool try_space = ref_total < ref_budget;
         if (try_space && pick.axis >= 0) {  // only where the object split's children overlap noticeably
             const Box ov = intersect(ol, orr);
-            try_space = valid(ov) && ov.half_area() > 1e-5f * root_area;
+            try_space = valid(ov) && ov.half_area() > alpha * root_area;
         }
         if (try_space) {
             const Choice sp = spatial_split(refs, box, pick.cost);
@@ -406,6 +407,7 @@ void HostScene::build_tree(int max_depth, bool verbose, bool spatial_splits)
         const char *budget = std::getenv("RT_SBVH_BUDGET");  // references allowed, as a multiple of the triangle count
         sb.ref_budget = (size_t)((budget ? std::atof(budget) : 1.5) * tri_count);
         sb.ref_total = (size_t)tri_count;
+        if (const char *al = std::getenv("RT_SBVH_ALPHA")) sb.alpha = (float)std::atof(al);
         sb.refine(0, refs, max_depth);
         std::vector<TriRecord> ordered(sb.leaf_order.size());
         std::vector<uint16_t> mats(spheres.size() + sb.leaf_order.size());
