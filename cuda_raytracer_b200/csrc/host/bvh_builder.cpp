@@ -161,7 +161,13 @@ struct Ref {
     Box box;
 };
 
-constexpr int kObjBins = 16, kSpaceBins = 32;
+#ifndef RT_SBVH_OBJ_BINS
+#define RT_SBVH_OBJ_BINS 16
+#endif
+#ifndef RT_SBVH_SPACE_BINS
+#define RT_SBVH_SPACE_BINS 32
+#endif
+constexpr int kObjBins = RT_SBVH_OBJ_BINS, kSpaceBins = RT_SBVH_SPACE_BINS;
 
 inline Box intersect(const Box &a, const Box &b)
 {
