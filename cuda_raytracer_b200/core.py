@@ -50,7 +50,8 @@ class SceneDesc(C.Structure):
 class RenderOpts(C.Structure):
     _fields_ = [("sort", C.c_int32), ("pass_spp", C.c_int32), ("pass_first", C.c_int32), ("pass_count", C.c_int32),
                 ("collect_stats", C.c_int32), ("stream_id", C.c_int32), ("sort_bits", C.c_int32), ("pass_group", C.c_int32),
-                ("reserved", C.c_int32)]
+                ("kernel_timing", C.c_int32), ("root_start", C.c_int32), ("single_pipe", C.c_int32), ("reserved", C.c_int32),
+                ("ray_first", C.c_int64), ("ray_count", C.c_int64)]
 
 
 class Stats(C.Structure):
@@ -71,7 +72,7 @@ class Stats(C.Structure):
 
 EXPORTS = [
     # rt_core.h
-    "rt_api_version", "rt_device_count", "rt_create", "rt_destroy", "rt_last_error", "rt_scene_upload", "rt_scene_set_image",
+    "rt_api_version", "rt_device_count", "rt_create", "rt_set_node_mode", "rt_get_node_mode", "rt_destroy", "rt_last_error", "rt_scene_upload", "rt_scene_set_image",
     "rt_render", "rt_render_device", "rt_postprocess", "rt_framebuffer_upload", "rt_trace_closest", "rt_generate_rays",
     "rt_process_rays", "rt_sort_pairs", "rt_scene_download_bvh", "rt_scene_bvh_device_ms", "rt_sort_device_ms", "rt_index_divide",
     # rt_scene.h
@@ -95,6 +96,8 @@ def lib():
     L.rt_last_error.restype = C.c_char_p
     L.rt_last_error.argtypes = [vp]
     L.rt_create.argtypes = [C.POINTER(vp), C.c_int]
+    L.rt_set_node_mode.argtypes = [vp, C.c_int]
+    L.rt_get_node_mode.argtypes = [vp]
     L.rt_destroy.argtypes = [vp]
     L.rt_destroy.restype = None
     L.rt_scene_upload.argtypes = [vp, C.POINTER(SceneDesc)]
@@ -223,11 +226,27 @@ def load_scene(path, use_bvh=True, verbose=False, cwd=None):
 class Renderer:
     """One render context bound to one CUDA device (rt_ctx)."""
 
-    def __init__(self, device=0):
+    NODE_MODES = {"f32": 0, "q16": 1, "w4": 2}
+
+    def __init__(self, device=0, nodes=None):
+        """nodes: None = the library's default (environment RT_NODES), else "f32" | "q16" | "w4" (rt_set_node_mode)."""
         self._ctx = C.c_void_p()
         _check(lib().rt_create(C.byref(self._ctx), device))
         self.width = self.height = 0
         self.last_stats = None
+        if nodes is not None:
+            self.set_node_mode(nodes)
+
+    def set_node_mode(self, nodes):
+        """Node format of the closest-hit kernel for the NEXT upload: "f32" (64-byte float records), "q16" (32-byte quantised
+        records of the same binary tree), "w4" (4-wide quantised nodes)."""
+        _check(lib().rt_set_node_mode(self._ctx, self.NODE_MODES[nodes] if isinstance(nodes, str) else int(nodes)), self._ctx)
+        return self
+
+    @property
+    def node_mode(self):
+        m = lib().rt_get_node_mode(self._ctx)
+        return {v: k for k, v in self.NODE_MODES.items()}.get(m, m)
 
     def close(self):
         if self._ctx:
@@ -253,27 +272,31 @@ class Renderer:
         return self
 
     @staticmethod
-    def _opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing=False, pass_group=0, root_start=False):
+    def _opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing=False, pass_group=0, root_start=False,
+              single_pipe=False, ray_first=0, ray_count=0):
         return RenderOpts(1 if sort else 0, pass_spp, pass_first, pass_count, 1 if collect_stats else 0, stream_id, sort_bits,
-                          pass_group, (1 if timing else 0) | (2 if root_start else 0))
+                          pass_group, 1 if timing else 0, 1 if root_start else 0, 1 if single_pipe else 0, 0, ray_first, ray_count)
 
     def render(self, sort=True, out=None, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0,
-               timing=False, pass_group=0, root_start=False):
+               timing=False, pass_group=0, root_start=False, single_pipe=False, ray_first=0, ray_count=0):
         """rt_render: host output (float32[H,W,3] un-normalised sums). ``out`` may be a preallocated (pinned) array.
-        ``root_start`` makes primary rays walk from the BVH root instead of their tile's entry records (same results)."""
+        ``root_start`` makes primary rays walk from the BVH root instead of their tile's entry records (same results);
+        ``ray_first`` / ``ray_count`` (> 0) select a range of the frame's ray sequence instead of whole passes."""
         if out is None:
             out = np.empty((self.height, self.width, 3), np.float32)
         assert out.dtype == np.float32 and out.size == self.width * self.height * 3 and out.flags.c_contiguous
-        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group, root_start)
+        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group, root_start,
+                       single_pipe, ray_first, ray_count)
         st = Stats()
         _check(lib().rt_render(self._ctx, C.byref(o), out.ctypes.data, C.byref(st)), self._ctx)
         self.last_stats = st
         return out
 
     def render_device(self, sort=True, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0,
-                      timing=False, pass_group=0, root_start=False):
+                      timing=False, pass_group=0, root_start=False, single_pipe=False, ray_first=0, ray_count=0):
         """rt_render_device: returns the device pointer (int) of the float32[H*W*3] framebuffer."""
-        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group, root_start)
+        o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group, root_start,
+                       single_pipe, ray_first, ray_count)
         st = Stats()
         ptr = C.c_void_p()
         _check(lib().rt_render_device(self._ctx, C.byref(o), C.byref(ptr), C.byref(st)), self._ctx)

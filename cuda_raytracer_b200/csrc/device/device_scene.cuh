@@ -72,8 +72,23 @@ __host__ __device__ __forceinline__ uint32_t fast_div(uint32_t n, const FastDiv 
 }
 #endif
 
+// Node formats the tracer can walk (rt_ctx::node_mode, environment RT_NODES; SURVEY §8f N3 "wider / compressed BVH"):
+//   kNodesF32  the 64-byte two-child record above: two LDG.256 per visit
+//   kNodesQ16  the SAME binary tree, each record compressed to 32 bytes = ONE LDG.256 per visit: the twelve bounds of the two
+//              children as 15-bit coordinates on a grid over the root box (rounded outwards + one cell of margin), two per
+//              word {lo | hi << 16}, words 0-2 = child 0 x/y/z, 3-5 = child 1, words 6-7 = the two child refs. Every stored
+//              16-bit value has its top bit set, so that ONE byte permute builds the float 1 + q / 32768 from it
+//              (0x3F000000 | v << 8) and the ray's sign picks the near / far bound in the same permute; t of a bound is one
+//              FFMA with per-ray constants (traverse.cuh, QuantRay).
+//   kNodesW4   a 4-wide tree collapsed from the binary one, 64 bytes per node = two kNodesQ16-style halves (children 0,1 and
+//              2,3 with their refs): two LDG.256 per visit, about half the visits.
+enum NodeMode : int { kNodesF32 = 0, kNodesQ16 = 1, kNodesW4 = 2 };
+
 struct DeviceScene {
     const float4 *nodes;      // 4 per internal record
+    const uint4 *qnodes;      // kNodesQ16: 2 per internal record (same numbering as `nodes`); kNodesW4: 4 per wide node
+    float q_scale[3];         // 32768 x cell size of the quantisation grid, per axis
+    float q_bias[3];          // grid origin - q_scale: coordinate = q_bias + (1 + q / 32768) * q_scale
     const float4 *tris;       // 4 per triangle (64-byte records)
     const float4 *materials;  // 3 per material
     const float4 *spheres;
@@ -118,6 +133,7 @@ struct BounceArgs {
     float *framebuffer;     // 3 floats per pixel, un-normalised sums
     uint32_t n_first;       // rays of the wave = group x pass_rays (bounce 0 only)
     uint32_t pass_rays;     // rays of ONE pass (pixels x rays_per_pixel); ray id = pass-in-wave x pass_rays + index in pass
+    uint32_t ray_offset;    // a wave that holds PART of one pass (rt_render_opts.ray_first / ray_count): index in pass = id + ray_offset
     int32_t bounce;
     int32_t rays_per_pixel; // of every pass of this wave
     FastDiv div_pass_rays, div_rays_per_pixel;
@@ -128,7 +144,6 @@ struct BounceArgs {
     uint32_t trace_batch, trace_refill_below, trace_node_min;  // TraceTuning
     const uint4 *entry_lists;  // per-tile entry records for primary rays (entry_lists.cuh), nullptr = start at the root
     int32_t entry_tiles_x;
-    int32_t stack_depth;    // entries per thread of the shared-memory traversal stack (= packed BVH depth, rounded up)
 };
 
 }  // namespace rtd

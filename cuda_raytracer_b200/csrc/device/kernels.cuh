@@ -20,11 +20,11 @@
 namespace rtd {
 
 constexpr int kBlock = 128;        // threads per CTA of the traversal kernels
-constexpr int kBlocksPerSM = 6;       // shared-memory stack variant: 6 x 32 KB at full depth
+constexpr int kBlocksPerSM = 6;       // process_kernel (parity hook): full-depth stack in shared memory, 6 x 32 KB
 #ifndef RT_TRACE_CTAS
-#define RT_TRACE_CTAS 8
+#define RT_TRACE_CTAS 9
 #endif
-constexpr int kBlocksPerSMLocal = RT_TRACE_CTAS;  // local-memory stack variant: 8 -> 32 warps per SM, <= 64 registers per thread
+constexpr int kBlocksPerSMLocal = RT_TRACE_CTAS;  // tracer: 8 CTAs -> 32 warps per SM, <= 64 registers per thread
 
 __device__ __forceinline__ uint32_t lanemask_lt() { return (1u << (threadIdx.x & 31)) - 1u; }
 
@@ -68,7 +68,7 @@ struct QueueTraceIO {
     {
         if (FIRST) {
             const uint32_t g = fast_div(i, a.div_pass_rays);  // pass of the wave; seeds and pixel follow the index inside that pass
-            if (!generate_ray(sc, i - g * a.pass_rays, a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d)) return false;
+            if (!generate_ray(sc, i - g * a.pass_rays + a.ray_offset, a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d)) return false;
         } else {
             const uint32_t slot = a.order ? __ldg(a.order + i) : i;
             const float4 ra = __ldcs(a.in.qa + slot), rb = __ldcs(a.in.qb + slot);
@@ -91,7 +91,7 @@ struct QueueTraceIO {
         cur = 0;
         if (!FIRST || !use_entries) return;
         const uint32_t g = fast_div(i, a.div_pass_rays);
-        const uint32_t pixel = fast_div(i - g * a.pass_rays, a.div_rays_per_pixel);
+        const uint32_t pixel = fast_div(i - g * a.pass_rays + a.ray_offset, a.div_rays_per_pixel);
         const uint32_t y = fast_div(pixel, sc.div_width), x = pixel - y * (uint32_t)sc.width;
         const uint4 *rec = a.entry_lists + 4 * (size_t)((y / kEntryTile) * (uint32_t)a.entry_tiles_x + x / kEntryTile);
         const uint4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2), q3 = __ldg(rec + 3);
@@ -122,21 +122,24 @@ __device__ __forceinline__ void flush_trace_counters(const TraceCounters &ctr, R
     }
 }
 
-template <bool FIRST, bool STATS, bool SMEM>
-__global__ void __launch_bounds__(kBlock, SMEM ? kBlocksPerSM : kBlocksPerSMLocal) trace_rays_kernel(const DeviceScene sc, const BounceArgs a)
+// Stack entries a thread may need: binary trees push one entry per level (+ the entry records of a primary ray); a 4-wide
+// node pushes up to three (rt_scene_upload checks the collapsed tree against kWideStackSlots).
+constexpr int kWideStackSlots = 72;
+template <int NODES>
+struct StackSlots {
+    static constexpr int value = NODES == kNodesW4 ? kWideStackSlots : kStackSlots;
+};
+
+template <bool FIRST, bool STATS, int NODES>
+__global__ void __launch_bounds__(kBlock, kBlocksPerSMLocal) trace_rays_kernel(const DeviceScene sc, const BounceArgs a)
 {
-    extern __shared__ uint32_t stack_smem[];
     const uint32_t n_in = FIRST ? a.n_first : a.pc->count[a.bounce];
     TraceCounters ctr;
-    QueueTraceIO<FIRST> io{sc, a, FIRST && !STATS && a.entry_lists != nullptr};  // the counting variant walks from the root
-    if (SMEM) {
-        SmemStack<kBlock> stack(stack_smem, a.stack_depth);
-        trace_persistent<STATS>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below, a.trace_node_min});
-    } else {
-        __shared__ uint2 stack_top[kStackTop > 0 ? kStackTop : 1][kBlock];
-        HybridStack<kBlock> stack(&stack_top[0][0]);
-        trace_persistent<STATS>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below, a.trace_node_min});
-    }
+    // the counting variant walks from the root; the entry records are cut from the binary tree's numbering
+    QueueTraceIO<FIRST> io{sc, a, FIRST && !STATS && NODES != kNodesW4 && a.entry_lists != nullptr};
+    __shared__ uint2 stack_top[kStackTop > 0 ? kStackTop : 1][kBlock];
+    HybridStack<kBlock, StackSlots<NODES>::value> stack(&stack_top[0][0]);
+    trace_persistent<STATS, NODES>(sc, n_in, &a.pc->cursor[a.bounce], stack, io, ctr, TraceTuning{a.trace_batch, a.trace_refill_below, a.trace_node_min});
     flush_trace_counters<STATS>(ctr, a.totals);
 }
 
@@ -206,7 +209,7 @@ __global__ void RT_SHADE_BOUNDS shade_kernel(const DeviceScene sc, const BounceA
         if (active) {
             if (FIRST) {
                 const uint32_t g = fast_div(id, a.div_pass_rays);
-                active = generate_ray(sc, id - g * a.pass_rays, a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d);
+                active = generate_ray(sc, id - g * a.pass_rays + a.ray_offset, a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d);
             } else {
                 o = f3(cur.ra.x, cur.ra.y, cur.ra.z);
                 d = f3(cur.ra.w, cur.rb.x, cur.rb.y);
@@ -221,7 +224,7 @@ __global__ void RT_SHADE_BOUNDS shade_kernel(const DeviceScene sc, const BounceA
             const float2 h = cur.h;
             const float closest = h.x;
             const int prim = __float_as_int(h.y);
-            const uint32_t g = fast_div(id, a.div_pass_rays), index = id - g * a.pass_rays;  // pass of the wave, ray index inside it
+            const uint32_t g = fast_div(id, a.div_pass_rays), index = id - g * a.pass_rays + a.ray_offset;  // pass of the wave, ray index inside it
             pixel = fast_div(index, a.div_rays_per_pixel);
             if (prim < 0) {
                 radiance = shade_miss(sc, d) * T;
@@ -303,23 +306,17 @@ struct Rays6IO {  // rt_trace_closest: rays {o, d} in, {prim, t} out
     }
 };
 
-template <bool STATS, bool SMEM>
-__global__ void __launch_bounds__(kBlock, SMEM ? kBlocksPerSM : kBlocksPerSMLocal) trace_kernel(const DeviceScene sc, const float *__restrict__ rays6, uint32_t n,
-                                                                      int with_spheres, int *__restrict__ out_prim,
-                                                                      float *__restrict__ out_t, uint32_t *cursor, int stack_depth,
-                                                                      TraceTuning tune, RenderTotals *totals)
+template <bool STATS, int NODES>
+__global__ void __launch_bounds__(kBlock, kBlocksPerSMLocal) trace_kernel(const DeviceScene sc, const float *__restrict__ rays6, uint32_t n,
+                                                                         int with_spheres, int *__restrict__ out_prim,
+                                                                         float *__restrict__ out_t, uint32_t *cursor,
+                                                                         TraceTuning tune, RenderTotals *totals)
 {
-    extern __shared__ uint32_t stack_smem[];
     TraceCounters ctr;
     Rays6IO io{sc, rays6, with_spheres, out_prim, out_t};
-    if (SMEM) {
-        SmemStack<kBlock> stack(stack_smem, stack_depth);
-        trace_persistent<STATS>(sc, n, cursor, stack, io, ctr, tune);
-    } else {
-        __shared__ uint2 stack_top[kStackTop > 0 ? kStackTop : 1][kBlock];
-        HybridStack<kBlock> stack(&stack_top[0][0]);
-        trace_persistent<STATS>(sc, n, cursor, stack, io, ctr, tune);
-    }
+    __shared__ uint2 stack_top[kStackTop > 0 ? kStackTop : 1][kBlock];
+    HybridStack<kBlock, StackSlots<NODES>::value> stack(&stack_top[0][0]);
+    trace_persistent<STATS, NODES>(sc, n, cursor, stack, io, ctr, tune);
     flush_trace_counters<STATS>(ctr, totals);
 }
 

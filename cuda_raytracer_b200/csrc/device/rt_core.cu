@@ -15,6 +15,7 @@
 #include "bvh_build.cuh"
 #include "kernels.cuh"
 #include "radix_sort.cuh"
+#include "wide_nodes.cuh"
 
 namespace rt {
 void set_global_error(const std::string &msg);  // scene_api.cpp
@@ -66,7 +67,11 @@ struct rt_ctx {
     RayQueue queue[2] = {};
     float2 *d_hits = nullptr;  // {t, prim} per queue position of the bounce in flight
     size_t queue_capacity = 0;
-    int stack_mode = 1;        // 1 = local-memory traversal stack (default: +5 %, leaves the L1 to the BVH), 0 = shared memory (RT_STACK=smem)
+    int node_mode = kNodesF32; // node format the tracer walks (rt_set_node_mode, environment RT_NODES = f32 | q16 | w4)
+    int active_nodes = kNodesF32;  // format of the uploaded scene (falls back to f32 when the grid cannot hold the scene)
+    void *d_qnodes = nullptr;  // compressed nodes (kNodesQ16: 32 B per record; kNodesW4: 64 B per wide node)
+    size_t cap_qnodes = 0;
+    int wide_nodes = 0, wide_depth = 0, wide_stack_need = 0;
     uint32_t trace_batch = kBatch, trace_refill_below = kRefillBelow, trace_node_min = kNodeMin;  // RT_BATCH / RT_REFILL override
     uint32_t *d_keys[2] = {nullptr, nullptr}, *d_vals[2] = {nullptr, nullptr};
     size_t sort_capacity = 0;
@@ -75,7 +80,7 @@ struct rt_ctx {
     PassCounters *d_pc = nullptr;
     RenderTotals *d_totals = nullptr;
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
-    std::vector<cudaEvent_t> ev_pool;  // per-launch timing (rt_render_opts.reserved & 1)
+    std::vector<cudaEvent_t> ev_pool;  // per-launch timing (rt_render_opts.kernel_timing)
 };
 
 namespace {
@@ -280,7 +285,7 @@ extern "C" int rt_create(rt_ctx **out, int device)
     if (const char *e = std::getenv("RT_PIPES")) ctx->pipes = std::min((int)rt_ctx::kMaxPipes, std::max(1, std::atoi(e)));
     if (const char *e = std::getenv("RT_TRACE_PER_SM")) ctx->trace_per_sm = std::max(0, std::atoi(e));
     if (const char *e = std::getenv("RT_SHADE_PER_SM")) ctx->shade_per_sm = std::max(0, std::atoi(e));
-    if (const char *e = std::getenv("RT_STACK")) ctx->stack_mode = std::strcmp(e, "local") == 0 ? 1 : 0;
+    if (const char *e = std::getenv("RT_NODES")) ctx->node_mode = std::strcmp(e, "q16") == 0 ? kNodesQ16 : std::strcmp(e, "w4") == 0 ? kNodesW4 : kNodesF32;
     if (const char *e = std::getenv("RT_ENTRY_K")) ctx->entry_max = std::min((int)kEntryMax, std::max(0, std::atoi(e)));
     if (const char *e = std::getenv("RT_BATCH")) ctx->trace_batch = (uint32_t)std::min(4096, std::max(4, std::atoi(e)));
     if (const char *e = std::getenv("RT_NODEMIN")) ctx->trace_node_min = (uint32_t)std::min(33, std::max(0, std::atoi(e)));
@@ -293,6 +298,14 @@ extern "C" int rt_create(rt_ctx **out, int device)
     return RT_OK;
 }
 
+extern "C" int rt_set_node_mode(rt_ctx *ctx, int mode)
+{
+    if (!ctx || mode < kNodesF32 || mode > kNodesW4) return fail(ctx, RT_ERR_INVALID, "rt_set_node_mode: mode must be 0 (f32), 1 (q16) or 2 (w4)");
+    ctx->node_mode = mode;
+    return RT_OK;
+}
+extern "C" int rt_get_node_mode(const rt_ctx *ctx) { return ctx ? (ctx->has_scene ? ctx->active_nodes : ctx->node_mode) : RT_ERR_INVALID; }
+
 extern "C" void rt_destroy(rt_ctx *ctx)
 {
     if (!ctx) return;
@@ -300,7 +313,7 @@ extern "C" void rt_destroy(rt_ctx *ctx)
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     for (cudaStream_t s : ctx->side) if (s) cudaStreamSynchronize(s);
     release(ctx->d_nodes); release(ctx->d_tris); release(ctx->d_materials); release(ctx->d_spheres); release(ctx->d_env);
-    release(ctx->d_matidx); release(ctx->d_raw); release(ctx->d_build); if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    release(ctx->d_matidx); release(ctx->d_qnodes); release(ctx->d_raw); release(ctx->d_build); if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     release(ctx->d_fb); release(ctx->d_fb_tmp); release(ctx->d_fb_tmp2); release(ctx->d_rgb8);
     for (int i = 0; i < 2; i++) {
         release(ctx->queue[i].qa); release(ctx->queue[i].qb); release(ctx->queue[i].qc);
@@ -530,8 +543,45 @@ extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *s)
     // no synchronisation: copies from the caller's pageable arrays are staged by the runtime before the call returns,
     // and everything else is ordered on the context's stream ahead of the first render kernel
 
+    // compressed node formats: derived from the 64-byte records that are now in d_nodes
+    ctx->active_nodes = kNodesF32;
+    QuantGrid grid{};
+    if (ctx->node_mode != kNodesF32) {
+        const RefNode &root_box = packer.nodes[0];
+        grid = make_quant_grid(root_box.lo, root_box.hi);
+        if (grid.ok || s->triangle_count == 0) ctx->active_nodes = ctx->node_mode;
+    }
+    if (ctx->active_nodes == kNodesQ16) {
+        if ((rc = reserve(ctx, &ctx->d_qnodes, &ctx->cap_qnodes, (size_t)ctx->packed_nodes * 32)) != RT_OK) return rc;
+        quantize_records_kernel<<<(ctx->packed_nodes + 127) / 128, 128, 0, ctx->stream>>>((const float4 *)ctx->d_nodes, ctx->packed_nodes,
+                                                                                        (uint4 *)ctx->d_qnodes, grid);
+        RT_CUDA(ctx, cudaGetLastError());
+    } else if (ctx->active_nodes == kNodesW4) {
+        std::vector<float> fetched;
+        WideCollapse wide;
+        wide.grid = grid;
+        if (ctx->device_packed) {  // the records exist only on the device
+            fetched.resize((size_t)ctx->packed_nodes * 16);
+            RT_CUDA(ctx, cudaMemcpyAsync(fetched.data(), ctx->d_nodes, fetched.size() * sizeof(float), cudaMemcpyDeviceToHost, ctx->stream));
+            RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            wide.records = fetched.data();
+        } else {
+            wide.records = reinterpret_cast<const float *>(packer.out.data());
+        }
+        wide.run();
+        ctx->wide_nodes = (int)(wide.out.size() / 16);
+        ctx->wide_depth = wide.depth;
+        ctx->wide_stack_need = wide.stack_need;
+        if (wide.stack_need > kWideStackSlots) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: 4-wide tree needs more stack entries than the tracer has (72)");
+        RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // wide.out is pageable and dies with this call
+        if ((rc = upload(ctx, &ctx->d_qnodes, &ctx->cap_qnodes, wide.out.data(), wide.out.size() * sizeof(uint32_t))) != RT_OK) return rc;
+        RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+
     DeviceScene &d = ctx->ds;
     d.nodes = static_cast<const float4 *>(ctx->d_nodes);
+    d.qnodes = static_cast<const uint4 *>(ctx->d_qnodes);
+    for (int k = 0; k < 3; k++) { d.q_scale[k] = grid.scale[k]; d.q_bias[k] = grid.bias[k]; }
     d.tris = static_cast<const float4 *>(ctx->d_tris);
     d.materials = static_cast<const float4 *>(ctx->d_materials);
     d.spheres = static_cast<const float4 *>(ctx->d_spheres);
@@ -652,30 +702,31 @@ int enqueue_sort(rt_ctx *ctx, const uint32_t *count_ptr, size_t bound, int bits,
 // ---- the pass loop (gpu_raytrace, raytracing.cu:170-284) ------------------------------------------------------
 namespace {
 
-// Shared-memory bytes of the traversal stack for one CTA (0 for the local-memory variant).
-size_t stack_bytes(const rt_ctx *ctx) { return ctx->stack_mode ? 0 : (size_t)(std::max(4, ctx->packed_depth) + 8) * kBlock * 8; }
-
+template <bool FIRST, bool STATS>
+void launch_trace_nodes(const rt_ctx *ctx, cudaStream_t stream, int grid, const BounceArgs &a)
+{
+    switch (ctx->active_nodes) {
+    case kNodesQ16: trace_rays_kernel<FIRST, STATS, kNodesQ16><<<grid, kBlock, 0, stream>>>(ctx->ds, a); break;
+    case kNodesW4: trace_rays_kernel<FIRST, STATS, kNodesW4><<<grid, kBlock, 0, stream>>>(ctx->ds, a); break;
+    default: trace_rays_kernel<FIRST, STATS, kNodesF32><<<grid, kBlock, 0, stream>>>(ctx->ds, a); break;
+    }
+}
 template <bool FIRST>
 void launch_trace(const rt_ctx *ctx, cudaStream_t stream, bool stats, int grid, const BounceArgs &a)
 {
-    const size_t smem = stack_bytes(ctx);
-    if (ctx->stack_mode) {
-        if (stats) trace_rays_kernel<FIRST, true, false><<<grid, kBlock, 0, stream>>>(ctx->ds, a);
-        else trace_rays_kernel<FIRST, false, false><<<grid, kBlock, 0, stream>>>(ctx->ds, a);
-    } else {
-        if (stats) trace_rays_kernel<FIRST, true, true><<<grid, kBlock, smem, stream>>>(ctx->ds, a);
-        else trace_rays_kernel<FIRST, false, true><<<grid, kBlock, smem, stream>>>(ctx->ds, a);
-    }
+    if (stats) launch_trace_nodes<FIRST, true>(ctx, stream, grid, a);
+    else launch_trace_nodes<FIRST, false>(ctx, stream, grid, a);
 }
 
-// Persistent grid of the tracer: every SM filled to the occupancy the stack variant allows.
+// Persistent grid of the tracer: every SM filled to the occupancy the kernel variant allows.
 int trace_grid_size(rt_ctx *ctx, int *out)
 {
     int per_sm = 0;
-    if (ctx->stack_mode)
-        RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_rays_kernel<false, false, false>, kBlock, 0));
-    else
-        RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_rays_kernel<false, false, true>, kBlock, stack_bytes(ctx)));
+    switch (ctx->active_nodes) {
+    case kNodesQ16: RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_rays_kernel<false, false, kNodesQ16>, kBlock, 0)); break;
+    case kNodesW4: RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_rays_kernel<false, false, kNodesW4>, kBlock, 0)); break;
+    default: RT_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_rays_kernel<false, false, kNodesF32>, kBlock, 0)); break;
+    }
     if (ctx->trace_per_sm > 0) per_sm = std::min(per_sm, ctx->trace_per_sm);
     *out = ctx->sm_count * std::max(1, per_sm);
     return RT_OK;
@@ -693,10 +744,34 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     const size_t pixels = (size_t)ctx->ds.width * ctx->ds.height;
     if (pixels * (size_t)pass_spp >= (1ull << 31)) return fail(ctx, RT_ERR_INVALID, "rt_render: width*height*pass_spp must be < 2^31");
     const int total_passes = (ctx->ray_count + pass_spp - 1) / pass_spp;
-    const int pass_first = std::max(0, opts.pass_first);
-    const int pass_end = opts.pass_count > 0 ? std::min(total_passes, pass_first + opts.pass_count) : total_passes;
+    // The work of this call: SEGMENTS = rays [offset, offset + count) of a pass. Whole passes by default or by pass range; with
+    // ray_count > 0 a range of the frame's ray sequence, whose first and last pass may be partial (seeds are functions of
+    // the pass and the ray's index inside it: raytracing.cu:89,229,236, scene.cu:81).
+    struct Segment {
+        int pass;
+        uint32_t offset, count;
+    };
+    std::vector<Segment> segs;
+    auto spp_of = [&](int p) { return std::min(ctx->ray_count - p * pass_spp, pass_spp); };
+    if (opts.ray_count > 0) {
+        if (opts.ray_first < 0) return fail(ctx, RT_ERR_INVALID, "rt_render: ray_first must be >= 0");
+        int64_t start = 0;
+        const int64_t u0 = opts.ray_first, u1 = opts.ray_first + opts.ray_count;
+        for (int p = 0; p < total_passes && start < u1; p++) {
+            const int64_t n = (int64_t)pixels * spp_of(p);
+            const int64_t a = std::max(u0, start), b = std::min(u1, start + n);
+            if (b > a) segs.push_back(Segment{p, (uint32_t)(a - start), (uint32_t)(b - a)});
+            start += n;
+        }
+    } else {
+        const int pass_first = std::max(0, opts.pass_first);
+        const int pass_end = opts.pass_count > 0 ? std::min(total_passes, pass_first + opts.pass_count) : total_passes;
+        for (int p = pass_first; p < pass_end; p++) segs.push_back(Segment{p, 0u, (uint32_t)(pixels * (size_t)spp_of(p))});
+    }
+    auto whole = [&](const Segment &g) { return g.offset == 0 && (size_t)g.count == pixels * (size_t)spp_of(g.pass); };
+    const int n_segs = (int)segs.size();
     const bool collect = opts.collect_stats != 0;
-    const bool timing = (opts.reserved & 1) != 0;  // CUDA-event pair around every bounce kernel and every reorder pass
+    const bool timing = opts.kernel_timing != 0;  // CUDA-event pair around every bounce kernel and every reorder pass
     std::vector<int> ev_kind;                       // 0 = trace kernel, 1 = reorder, 2 = shade kernel
     std::vector<int> ev_bounce;
     int cur_bounce = 0;
@@ -732,7 +807,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         const size_t per_pass = pass_rays_max * (size_t)(88 + (sort ? 16 : 0));    // 2 x 40 B queues + 8 B hit (+ keys, permutation)
         max_group = (int)std::max<size_t>(1, (free_b + have) / 10 * 7 / std::max<size_t>(1, per_pass));
     }
-    max_group = std::max(1, std::min({max_group, (int)kMaxPassGroup, pass_end - pass_first}));
+    max_group = std::max(1, std::min({max_group, (int)kMaxPassGroup, std::max(1, n_segs)}));
     while (max_group > 1 && pass_rays_max * (size_t)max_group >= (1ull << 31)) max_group--;
     // PIPES (2 by default, RT_PIPES=1..4): consecutive waves rotate over that many streams, each with its own share of the queues and its own
     // counters. A wave is a chain of dependent launches whose late bounces hold a few 10^4 rays and whose persistent
@@ -740,9 +815,9 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     // its CTAs instead of idling, and the HBM-latency-bound shade kernel of one wave overlaps the issue-bound tracer of the
     // other. The automatic wave size is divided by the pipes so that the memory in use stays the same. Not with the reorder pass (its
     // scratch is single), not with per-kernel event timing or counting (their numbers are per kernel, alone on the GPU).
-    int pipes = (sort || timing || collect || (opts.reserved & 4) || pass_end - pass_first < 2) ? 1 : ctx->pipes;
-    pipes = std::min(pipes, pass_end - pass_first);
-    if (pipes > 1 && opts.pass_group <= 0) max_group = std::max(1, std::min(max_group / pipes, (pass_end - pass_first + pipes - 1) / pipes));
+    int pipes = (sort || timing || collect || opts.single_pipe || n_segs < 2) ? 1 : ctx->pipes;
+    pipes = std::max(1, std::min(pipes, n_segs));
+    if (pipes > 1 && opts.pass_group <= 0) max_group = std::max(1, std::min(max_group / pipes, (n_segs + pipes - 1) / pipes));
     // the automatic wave size is a guess at what the allocator will grant: on an out-of-memory answer try smaller waves
     for (;;) {
         rc = ensure_queues(ctx, pass_rays_max * (size_t)max_group * (size_t)pipes, sort);
@@ -761,7 +836,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
 
     // entry records of the primary rays: cut once per scene + camera, reused by every pass and frame
     const int tiles_x = (ctx->ds.width + kEntryTile - 1) / kEntryTile, tiles_y = (ctx->ds.height + kEntryTile - 1) / kEntryTile;
-    const bool use_entries = ctx->entry_max > 0 && (opts.reserved & 2) == 0;
+    const bool use_entries = ctx->entry_max > 0 && opts.root_start == 0;
     if (use_entries && ctx->entry_dirty) {
         if ((rc = reserve(ctx, &ctx->d_entry, &ctx->cap_entry, (size_t)tiles_x * tiles_y * 64)) != RT_OK) return rc;
         build_entry_lists_kernel<<<(tiles_x * tiles_y + 127) / 128, 128, 0, ctx->stream>>>(ctx->ds, tiles_x, tiles_y, ctx->entry_max, (uint4 *)ctx->d_entry);
@@ -781,14 +856,16 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     // A WAVE is `group` consecutive passes of equal size traced together: every pass keeps the reference's seeds
     // (they depend on the pass, not on the launch), while the late bounces - a few 10^4 rays per pass, latency-bound -
     // and the launch gaps are paid once per wave instead of once per pass.
-    for (int pass = pass_first; pass < pass_end;) {
-        const int rays_to_cast = std::min(ctx->ray_count - pass * pass_spp, pass_spp);
-        const uint32_t pass_rays = (uint32_t)(pixels * (size_t)rays_to_cast);
-        int group = 1;
-        while (group < max_group && pass + group < pass_end && std::min(ctx->ray_count - (pass + group) * pass_spp, pass_spp) == rays_to_cast)
+    for (int si = 0; si < n_segs;) {
+        const int pass = segs[si].pass;
+        const int rays_to_cast = spp_of(pass);
+        const bool partial = !whole(segs[si]);
+        const uint32_t pass_rays = partial ? segs[si].count : (uint32_t)(pixels * (size_t)rays_to_cast);
+        int group = 1;  // a partial pass is a wave of its own
+        while (!partial && group < max_group && si + group < n_segs && whole(segs[si + group]) && spp_of(segs[si + group].pass) == rays_to_cast)
             group++;
         int remaining[kMaxPassGroup];  // the reference's `remaining_rays` after the decrement (:224-225), per pass
-        for (int g = 0; g < group; g++) remaining[g] = ctx->ray_count - (pass + g) * pass_spp - rays_to_cast;
+        for (int g = 0; g < group; g++) remaining[g] = ctx->ray_count - segs[si + g].pass * pass_spp - rays_to_cast;
         const uint32_t total = pass_rays * (uint32_t)group;
         primaries += total;
         const int pipe = wave++ % pipes;
@@ -810,6 +887,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             a.framebuffer = ctx->d_fb;
             a.n_first = total;
             a.pass_rays = pass_rays;
+            a.ray_offset = partial ? segs[si].offset : 0u;
             a.bounce = b;
             a.rays_per_pixel = rays_to_cast;
             a.div_pass_rays = make_fast_div(pass_rays);
@@ -821,7 +899,6 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             a.pcg_inc = pcg_inc;
             a.key_bits = key_bits;
             a.hits = ctx->d_hits + qoff;
-            a.stack_depth = std::max(4, ctx->packed_depth) + 8;
             a.trace_batch = ctx->trace_batch;
             a.trace_refill_below = ctx->trace_refill_below;
             a.trace_node_min = ctx->trace_node_min;
@@ -849,7 +926,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             }
         }
         passes_done += group;
-        pass += group;
+        si += group;
     }
     if (pipes > 1) {
         for (int i = 0; i < pipes - 1; i++) {
@@ -979,18 +1056,16 @@ extern "C" int rt_trace_closest(rt_ctx *ctx, const float *rays6, int32_t n, int3
         int grid = 0, rc = trace_grid_size(ctx, &grid);
         if (rc != RT_OK) return rc;
         grid = (int)std::min<size_t>((size_t)grid, ((size_t)n + kBlock - 1) / kBlock);
-        const size_t smem = stack_bytes(ctx);
-        const int depth = std::max(4, ctx->packed_depth);
         uint32_t *cursor = &ctx->d_pc->cursor[0];
         const TraceTuning tune{ctx->trace_batch, ctx->trace_refill_below, ctx->trace_node_min};
         const float *r6 = (const float *)rays.p;
-        if (ctx->stack_mode) {
-            if (stats) trace_kernel<true, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->ds, r6, (uint32_t)n, with_spheres, (int *)prim.p, (float *)t.p, cursor, depth, tune, ctx->d_totals);
-            else trace_kernel<false, false><<<grid, kBlock, 0, ctx->stream>>>(ctx->ds, r6, (uint32_t)n, with_spheres, (int *)prim.p, (float *)t.p, cursor, depth, tune, ctx->d_totals);
-        } else {
-            if (stats) trace_kernel<true, true><<<grid, kBlock, smem, ctx->stream>>>(ctx->ds, r6, (uint32_t)n, with_spheres, (int *)prim.p, (float *)t.p, cursor, depth, tune, ctx->d_totals);
-            else trace_kernel<false, true><<<grid, kBlock, smem, ctx->stream>>>(ctx->ds, r6, (uint32_t)n, with_spheres, (int *)prim.p, (float *)t.p, cursor, depth, tune, ctx->d_totals);
+#define RT_TRACE_HOOK(STATS, NODES) trace_kernel<STATS, NODES><<<grid, kBlock, 0, ctx->stream>>>(ctx->ds, r6, (uint32_t)n, with_spheres, (int *)prim.p, (float *)t.p, cursor, tune, ctx->d_totals)
+        switch (ctx->active_nodes) {
+        case kNodesQ16: if (stats) RT_TRACE_HOOK(true, kNodesQ16); else RT_TRACE_HOOK(false, kNodesQ16); break;
+        case kNodesW4: if (stats) RT_TRACE_HOOK(true, kNodesW4); else RT_TRACE_HOOK(false, kNodesW4); break;
+        default: if (stats) RT_TRACE_HOOK(true, kNodesF32); else RT_TRACE_HOOK(false, kNodesF32); break;
         }
+#undef RT_TRACE_HOOK
     }
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
     RT_CUDA(ctx, cudaGetLastError());

@@ -132,6 +132,57 @@ __device__ __forceinline__ void intersect_spheres(const DeviceScene &sc, float3 
     }
 }
 
+// ---- quantised boxes (kNodesQ16 / kNodesW4, layout in device_scene.cuh) ------------------------------------------------
+// Per ray: t(bound) = f * a + b with f = 1 + q / 32768 the float a byte permute builds from the stored 16 bits,
+// a = q_scale / d and b = (q_bias - o) / d; `near` / `far` are the permute selectors that take the low or the high half
+// of a {lo | hi << 16} word according to the sign of the direction component (0x7104: bytes {K0, w0, w1, K3} of
+// {w, K = 0x3F000000}; 0x7324: {K0, w2, w3, K3}). Rounding: a and b carry a few ulp of (extent / d), i.e. ~1e-7 of the scene
+// extent in coordinates = 0.004 grid cells; the packer adds a whole cell of margin on every side, so the test is
+// conservative for origins up to ~100 scene extents away from the tree. An axis-parallel ray (1 / d = +-inf) yields
+// NaN = "no constraint on this axis", as with RT_SLAB_FMA. Hits always come from the exact triangle test.
+struct QuantRay {
+    float ax, ay, az, bx, by, bz;
+    uint32_t nx, ny, nz, fx, fy, fz;
+};
+__device__ __forceinline__ QuantRay quant_ray(const DeviceScene &sc, float3 o, float3 inv)
+{
+    QuantRay q;
+    q.ax = sc.q_scale[0] * inv.x; q.ay = sc.q_scale[1] * inv.y; q.az = sc.q_scale[2] * inv.z;
+    q.bx = (sc.q_bias[0] - o.x) * inv.x; q.by = (sc.q_bias[1] - o.y) * inv.y; q.bz = (sc.q_bias[2] - o.z) * inv.z;
+    q.nx = __float_as_int(inv.x) < 0 ? 0x7324u : 0x7104u; q.fx = q.nx ^ 0x0220u;
+    q.ny = __float_as_int(inv.y) < 0 ? 0x7324u : 0x7104u; q.fy = q.ny ^ 0x0220u;
+    q.nz = __float_as_int(inv.z) < 0 ? 0x7324u : 0x7104u; q.fz = q.nz ^ 0x0220u;
+    return q;
+}
+// (prmt.b32 directly: __byte_perm masks its selector with 0x7777 first, one LOP3 per selector and visit)
+__device__ __forceinline__ float quant_f(uint32_t w, uint32_t sel)
+{
+    float f;
+    asm("prmt.b32 %0, %1, 0x3F000000, %2;" : "=f"(f) : "r"(w), "r"(sel));
+    return f;
+}
+// one child: wx / wy / wz = its {lo | hi << 16} words
+__device__ __forceinline__ bool slab_q(uint32_t wx, uint32_t wy, uint32_t wz, const QuantRay &q, float limit, float &t_enter)
+{
+    const float tn = fmaxf(fmaxf(__fmaf_rn(quant_f(wx, q.nx), q.ax, q.bx), __fmaf_rn(quant_f(wy, q.ny), q.ay, q.by)),
+                           fmaxf(__fmaf_rn(quant_f(wz, q.nz), q.az, q.bz), 0.0f));
+    const float tf = fminf(fminf(__fmaf_rn(quant_f(wx, q.fx), q.ax, q.bx), __fmaf_rn(quant_f(wy, q.fy), q.ay, q.by)),
+                           fminf(__fmaf_rn(quant_f(wz, q.fz), q.az, q.bz), limit));
+    t_enter = tn;
+    return tn <= tf;
+}
+struct __align__(32) Uint8 {
+    uint4 lo, hi;
+};
+__device__ __forceinline__ Uint8 ldg256u(const void *p)
+{
+    Uint8 r;
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w)
+                 : "l"(p));
+    return r;
+}
+
 // RT_FAST_RCP (default 1): 1 / a of the triangle test through MUFU.RCP alone (rcp.approx, <= 1 ulp, subnormal inputs
 // handled) instead of the IEEE division sequence (range check + 3 fix-up instructions + a slow-path call): u, v and t
 // move by at most an ulp, far inside the 1e-5 relative bar on t; the reference's own GPU build divides with
@@ -247,32 +298,26 @@ struct TraceTuning {
     uint32_t node_min;      // leave the descent loop when fewer lanes than this are still descending
 };
 
-// Stack storage policies. Both are entry-major per warp so the 32 lanes of an access hit 32 banks / one 128-byte line.
-template <int BLOCK>
-struct SmemStack {
-    uint32_t *ref;
-    float *dist;
-    __device__ __forceinline__ SmemStack(uint32_t *base, int depth) : ref(base + threadIdx.x), dist(reinterpret_cast<float *>(base) + (size_t)depth * BLOCK + threadIdx.x) {}
-    __device__ __forceinline__ void push(int sp, uint32_t r, float d) { ref[sp * BLOCK] = r; dist[sp * BLOCK] = d; }
-    __device__ __forceinline__ void get(int sp, uint32_t &r, float &d) const { r = ref[sp * BLOCK]; d = dist[sp * BLOCK]; }
-};
 #ifndef RT_STACK_TOP
 #define RT_STACK_TOP 8
 #endif
 constexpr int kStackTop = RT_STACK_TOP;  // entries per thread kept in shared memory; deeper ones go to local memory
 
-// Default stack: the first kStackTop entries of every thread live in shared memory ([entry][thread]: the 32 lanes of
+// Traversal stack: the first kStackTop entries of every thread live in shared memory ([entry][thread]: the 32 lanes of
 // a warp hit 32 banks whatever their individual depths are, one data-pipe wavefront per access), the rest in a
 // thread-local array. A purely local stack scatters: lanes at different depths touch different 128-byte lines, and
 // ncu showed those accesses as 28 % of the L1 data-pipe load of the tracer (profiles/r1c). 8 entries x 128 threads x
-// 8 B = 8 KB per CTA leaves the L1 to the BVH, unlike a full-depth shared stack (SmemStack).
-template <int BLOCK>
+// 8 B = 8 KB per CTA leaves the L1 to the BVH, unlike a full-depth shared stack (measured in round 1: -5 %, removed).
+template <int BLOCK, int SLOTS = kStackSlots>
 struct HybridStack {
     // shared-window address of smem[0][threadIdx.x], taken once: through a generic pointer the compiler re-derives the
     // window base (S2R SR_CgaCtaId + 2 integer ops) at every push and pop
     uint32_t top;
-    uint2 deep[kStackSlots - kStackTop > 0 ? kStackSlots - kStackTop : 1];
-    __device__ __forceinline__ explicit HybridStack(uint2 *smem) : top((uint32_t)__cvta_generic_to_shared(smem + threadIdx.x)) {}
+    uint2 deep[SLOTS - kStackTop > 0 ? SLOTS - kStackTop : 1];
+    __device__ __forceinline__ explicit HybridStack(uint2 *smem) : top((uint32_t)__cvta_generic_to_shared(smem + threadIdx.x))
+    {
+        asm volatile("" : "+r"(top));  // opaque: otherwise ptxas may rematerialise the address (S2UR + S2R + 3 ALU ops) at every visit
+    }
     __device__ __forceinline__ void push(int sp, uint32_t r, float d)
     {
         if (sp < kStackTop)
@@ -292,7 +337,7 @@ struct HybridStack {
     }
 };
 
-template <bool STATS, class Stack, class IO>
+template <bool STATS, int NODES, class Stack, class IO>
 __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t n, uint32_t *cursor, Stack &stack, IO &io,
                                                  TraceCounters &ctr, TraceTuning tune)
 {
@@ -319,6 +364,8 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
     float closest = kMissT;
     float3 o = f3(0, 0, 0), d = f3(0, 0, 1), inv = f3(0, 0, 1), so = f3(0, 0, 0);
     RaySigns sg = ray_signs(inv);
+    QuantRay qr = quant_ray(sc, o, inv);
+    const uint4 *__restrict__ qnodes = sc.qnodes;
 
     for (;;) {
         // ---- refill: all 32 lanes are here ----
@@ -341,8 +388,12 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
                 prim = -1;
                 if (io.load(slot, o, d, closest, prim)) {
                     inv = f3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-                    sg = ray_signs(inv);
-                    so = slab_origin(o, inv);
+                    if (NODES == kNodesF32) {
+                        sg = ray_signs(inv);
+                        so = slab_origin(o, inv);
+                    } else {
+                        qr = quant_ray(sc, o, inv);
+                    }
                     io.begin(slot, stack, sp, cur);  // record 0 (the root), or the tile's entry records for primary rays
                     busy = true;
                 }
@@ -362,32 +413,71 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
         while (busy) {
             // descend through internal records until this lane holds a leaf (or runs dry)
             while (!(cur & kLeafBit)) {
-                const float4 *nd = nodes + 4 * (size_t)cur;
-                // One 32-byte half per child (box + ref). Fetching the halves in opposite order on odd and even lanes
-                // (to spread one LDG.256 over all four sector positions of the L1 lines) was measured: no gain, and
-                // it makes tie-breaking lane-dependent, so every lane reads child 0 first.
-                const Float8 na = ldg256(nd), nb = ldg256(nd + 2);
-                const uint2 q3 = make_uint2(__float_as_uint(na.hi.z), __float_as_uint(nb.hi.z));
                 if (STATS) ctr.internal_visits++;
-                float d0, d1;
-                const bool h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, so, inv, sg, closest, d0);
-                const bool h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, so, inv, sg, closest, d1);
-                if (h0 && h1) {
-                    const bool zero_near = d0 < d1;
-                    stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
-                    sp++;
-                    cur = zero_near ? q3.x : q3.y;
-                } else if (h0) {
-                    cur = q3.x;
-                } else if (h1) {
-                    cur = q3.y;
+                if (NODES == kNodesW4) {
+                    // 4-wide node: two 32-byte halves {children 0,1} {children 2,3}; hit children sorted by entry distance
+                    // (5 compare-exchanges), the nearest becomes the current reference, the others go on the stack far first
+                    const uint4 *nd = qnodes + 4 * (size_t)cur;
+                    const Uint8 na = ldg256u(nd), nb = ldg256u(nd + 2);
+                    constexpr float kNoHit = 3e38f;
+                    float e0, e1, e2, e3;
+                    const bool h0 = slab_q(na.lo.x, na.lo.y, na.lo.z, qr, closest, e0), h1 = slab_q(na.lo.w, na.hi.x, na.hi.y, qr, closest, e1);
+                    const bool h2 = slab_q(nb.lo.x, nb.lo.y, nb.lo.z, qr, closest, e2), h3 = slab_q(nb.lo.w, nb.hi.x, nb.hi.y, qr, closest, e3);
+                    float k0 = h0 ? e0 : kNoHit, k1 = h1 ? e1 : kNoHit, k2 = h2 ? e2 : kNoHit, k3 = h3 ? e3 : kNoHit;
+                    uint32_t r0 = na.hi.z, r1 = na.hi.w, r2 = nb.hi.z, r3 = nb.hi.w;
+                    const int hits = (int)h0 + (int)h1 + (int)h2 + (int)h3;
+#define RT_CSWAP(ka, ra, kb, rb) { const bool sw = kb < ka; const float tk = sw ? ka : kb; ka = sw ? kb : ka; kb = tk; const uint32_t tr = sw ? ra : rb; ra = sw ? rb : ra; rb = tr; }
+                    RT_CSWAP(k0, r0, k1, r1) RT_CSWAP(k2, r2, k3, r3) RT_CSWAP(k0, r0, k2, r2) RT_CSWAP(k1, r1, k3, r3) RT_CSWAP(k1, r1, k2, r2)
+#undef RT_CSWAP
+                    if (hits > 3) { stack.push(sp, r3, k3); sp++; }
+                    if (hits > 2) { stack.push(sp, r2, k2); sp++; }
+                    if (hits > 1) { stack.push(sp, r1, k1); sp++; }
+                    if (hits > 0) {
+                        cur = r0;
+                    } else {
+                        float entry;
+                        do {
+                            if (sp == 0) { cur = kDoneRef; break; }
+                            sp--;
+                            stack.get(sp, cur, entry);
+                        } while (entry >= closest);
+                    }
                 } else {
-                    float entry;
-                    do {
-                        if (sp == 0) { cur = kDoneRef; break; }
-                        sp--;
-                        stack.get(sp, cur, entry);
-                    } while (entry >= closest);
+                    float d0, d1;
+                    bool h0, h1;
+                    uint2 q3;
+                    if (NODES == kNodesQ16) {  // one 32-byte record: 12 bounds on the 15-bit grid + the two child refs
+                        const Uint8 nq = ldg256u(qnodes + 2 * (size_t)cur);
+                        q3 = make_uint2(nq.hi.z, nq.hi.w);
+                        h0 = slab_q(nq.lo.x, nq.lo.y, nq.lo.z, qr, closest, d0);
+                        h1 = slab_q(nq.lo.w, nq.hi.x, nq.hi.y, qr, closest, d1);
+                    } else {
+                        const float4 *nd = nodes + 4 * (size_t)cur;
+                        // One 32-byte half per child (box + ref). Fetching the halves in opposite order on odd and even lanes
+                        // (to spread one LDG.256 over all four sector positions of the L1 lines) was measured: no gain, and
+                        // it makes tie-breaking lane-dependent, so every lane reads child 0 first.
+                        const Float8 na = ldg256(nd), nb = ldg256(nd + 2);
+                        q3 = make_uint2(__float_as_uint(na.hi.z), __float_as_uint(nb.hi.z));
+                        h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, so, inv, sg, closest, d0);
+                        h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, so, inv, sg, closest, d1);
+                    }
+                    if (h0 && h1) {
+                        const bool zero_near = d0 < d1;
+                        stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
+                        sp++;
+                        cur = zero_near ? q3.x : q3.y;
+                    } else if (h0) {
+                        cur = q3.x;
+                    } else if (h1) {
+                        cur = q3.y;
+                    } else {
+                        float entry;
+                        do {
+                            if (sp == 0) { cur = kDoneRef; break; }
+                            sp--;
+                            stack.get(sp, cur, entry);
+                        } while (entry >= closest);
+                    }
                 }
                 // lanes that already hold a leaf wait at the loop exit: stop descending once only a few are left
                 if (__popc(__activemask()) < node_min) break;

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define RT_API_VERSION 5
+#define RT_API_VERSION 6
 
 typedef enum rt_status {
     RT_OK = 0,
@@ -82,9 +82,16 @@ typedef struct rt_render_opts {
     int32_t pass_group;    /* passes traced together as one wave: 0 = auto (memory budget, at most 16), 1 = one pass per wave as the
                               reference does. Results do not depend on it beyond float summation order. With sort = 0 two
                               waves are in flight at a time on two streams of the context (environment RT_PIPES=1: one). */
-    int32_t reserved;      /* bit 0: time every bounce kernel / reorder pass with CUDA events (rt_stats.trace_ms, shade_ms, sort_ms);
-                            *        one wave at a time, so that every interval is one kernel's own;
-                            * bit 1: primary rays walk from the BVH root instead of their screen tile's entry records (same results) */
+    int32_t kernel_timing; /* 1 = CUDA-event pair around every bounce kernel / reorder pass (rt_stats.trace_ms, shade_ms, sort_ms); one
+                              wave at a time, so that every interval is one kernel's own */
+    int32_t root_start;    /* 1 = primary rays walk from the BVH root instead of their screen tile's entry records (same results) */
+    int32_t single_pipe;   /* 1 = one wave at a time on one stream (as RT_PIPES=1) */
+    int32_t reserved;      /* must be 0 */
+    int64_t ray_first;     /* with ray_count > 0: render only rays [ray_first, ray_first + ray_count) of the frame's ray sequence */
+    int64_t ray_count;     /* (pass 0's rays, then pass 1's, ...; a pass holds width*height*spp_of_that_pass rays, pixel-major) and
+                              ignore pass_first / pass_count. A ray's seeds depend on its pass and its index inside the pass
+                              (raytracing.cu:89,229,236, scene.cu:81), so disjoint ranges add up to the whole frame exactly as
+                              disjoint pass ranges do; used for the per-GPU split when the pass count does not divide. */
 } rt_render_opts;
 
 typedef struct rt_stats {
@@ -111,6 +118,14 @@ int rt_api_version(void);
 int rt_device_count(void);
 /* device: CUDA ordinal (honours CUDA_VISIBLE_DEVICES). */
 int rt_create(rt_ctx **out, int device);
+/* Node format the closest-hit kernel walks, takes effect at the next rt_scene_upload:
+ *   0 = 64-byte two-child records with float boxes (two 256-bit loads per visit);
+ *   1 = the same binary tree, 32-byte records with 15-bit quantised boxes (one 256-bit load per visit);
+ *   2 = 4-wide nodes collapsed from that tree, 64 bytes, quantised boxes.
+ * Same hits in every mode (boxes only grow; hits come from the exact triangle test). Default: environment RT_NODES
+ * (f32 | q16 | w4), else the library's default. rt_get_node_mode returns the format of the uploaded scene. */
+int rt_set_node_mode(rt_ctx *ctx, int mode);
+int rt_get_node_mode(const rt_ctx *ctx);
 void rt_destroy(rt_ctx *ctx);
 /* ctx may be NULL for errors of rt_create / the host scene layer (thread-local). */
 const char *rt_last_error(const rt_ctx *ctx);

@@ -89,6 +89,7 @@ def port():
         L.oracle_gpu_proc_seed.argtypes = [C.c_int32, C.c_int32]
         L.oracle_gpu_proc_seed.restype = C.c_uint32
         L.oracle_closest_hit.argtypes = [S, f32p, C.c_int, C.c_int, f32p, i32p, C.POINTER(Counters)]
+        L.oracle_closest_hit_ex.argtypes = [S, f32p, C.c_int, C.c_int, C.c_int, f32p, i32p, C.POINTER(Counters)]
         L.oracle_generate.argtypes = [S, f32p, C.c_int, C.c_int, C.c_int, C.c_int]
         L.oracle_process.argtypes = [S, f32p, u32p, C.c_int]
         L.oracle_render.argtypes = [S, C.c_int, C.c_int, C.c_int, f32p, C.POINTER(Counters)]

@@ -218,8 +218,39 @@ static void bvh_closest_hit(const oracle_scene *s, v3 o, v3 d, int near_first, f
     }
 }
 
+/* ---- scene.cu:338-372: the sphere loop of process_ray; runs BEFORE the BVH and seeds closest / closest_idx ---------- */
+static inline void sphere_closest_hit(const oracle_scene *s, v3 origin, v3 dir, float *closest_io, int32_t *idx_io)
+{
+    float closest = *closest_io;
+    int32_t closest_idx = *idx_io;
+    for (int i = 0; i < s->sphere_count; i++) {
+        v3 center = ld3(s->spheres + 4 * i);
+        float radius = s->spheres[4 * i + 3];
+        v3 offset = sub3(center, origin);
+        float minus_half_b = dot3(offset, dir);
+        float quarter_c = magsq3(offset) - radius * radius;
+        float quarter_disc = minus_half_b * minus_half_b - quarter_c;
+        if (quarter_disc < 0) continue;
+        float half_root = sqrtf(quarter_disc);
+        float t = minus_half_b - half_root;
+        if (t < closest && (double)t >= 0.005) { closest = t; closest_idx = i; continue; }
+        t = minus_half_b + half_root;
+        if (t < closest && (double)t >= 0.005) { closest = t; closest_idx = i; continue; }
+    }
+    *closest_io = closest;
+    *idx_io = closest_idx;
+}
+
 void oracle_closest_hit(const oracle_scene *s, const float *rays6, int n, int near_first, float *out_t, int32_t *out_idx,
                         oracle_counters *counters)
+{
+    oracle_closest_hit_ex(s, rays6, n, near_first, 0, out_t, out_idx, counters);
+}
+
+/* The closest-hit query of process_ray as a whole: sphere loop (scene.cu:338-372) when with_spheres, then the BVH
+ * (scene.cu:134-241) continuing from the sphere result. */
+void oracle_closest_hit_ex(const oracle_scene *s, const float *rays6, int n, int near_first, int with_spheres, float *out_t,
+                           int32_t *out_idx, oracle_counters *counters)
 {
     int64_t iv = 0, lv = 0, tt = 0;
 #pragma omp parallel for schedule(dynamic, 1024) reduction(+ : iv, lv, tt)
@@ -227,6 +258,7 @@ void oracle_closest_hit(const oracle_scene *s, const float *rays6, int n, int ne
         oracle_counters c = {0, 0, 0, 0};
         float t = 1e30f;
         int32_t idx = -1;
+        if (with_spheres) sphere_closest_hit(s, ld3(rays6 + 6 * (size_t)i), ld3(rays6 + 6 * (size_t)i + 3), &t, &idx);
         bvh_closest_hit(s, ld3(rays6 + 6 * (size_t)i), ld3(rays6 + 6 * (size_t)i + 3), near_first, &t, &idx, counters ? &c : NULL);
         out_t[i] = t;
         out_idx[i] = idx;
@@ -273,20 +305,7 @@ static int process_one(const oracle_scene *s, float *rd, pcg rng, oracle_counter
     float closest = 1e30f;
     int32_t closest_idx = -1;
 
-    for (int i = 0; i < s->sphere_count; i++) { /* scene.cu:338-372 */
-        v3 center = ld3(s->spheres + 4 * i);
-        float radius = s->spheres[4 * i + 3];
-        v3 offset = sub3(center, origin);
-        float minus_half_b = dot3(offset, dir);
-        float quarter_c = magsq3(offset) - radius * radius;
-        float quarter_disc = minus_half_b * minus_half_b - quarter_c;
-        if (quarter_disc < 0) continue;
-        float half_root = sqrtf(quarter_disc);
-        float t = minus_half_b - half_root;
-        if (t < closest && (double)t >= 0.005) { closest = t; closest_idx = i; continue; }
-        t = minus_half_b + half_root;
-        if (t < closest && (double)t >= 0.005) { closest = t; closest_idx = i; continue; }
-    }
+    sphere_closest_hit(s, origin, dir, &closest, &closest_idx);
 
     bvh_closest_hit(s, origin, dir, 0, &closest, &closest_idx, c);
 

@@ -102,16 +102,48 @@ def test_closest_hit_edge_cases(renderer):
     assert len(p0) == 0 and len(t0) == 0
 
 
-def test_closest_hit_with_spheres(renderer):
-    scene, A = _setup(renderer, "cornell_plus")
+@pytest.mark.parametrize("name", ["spheres", "cornell_plus"])
+def test_closest_hit_with_spheres(renderer, name):
+    """Sphere loop (scene.cu:338-372) + BVH as one query, against the oracle's sphere leg (pinned to the reference's golden
+    process_ray records, tests/test_oracle_golden.py): primary rays, rays that START ON a sphere (bounce 1, incl. rays inside
+    the glass sphere of cornell_plus), and random rays; spheres.scene holds the radius-40000 spheres 4e5 away, where the
+    discriminant cancels in FP32. Bar: primitive equal unless t ties within 1e-5 relative; t within 1e-5 relative, plus for
+    sphere hits 2 ulp of |b| (the root b -+ sqrt(disc) subtracts two numbers of the size of the distance to the centre:
+    an FMA-contracted discriminant moves the root by ulps of b, not of t)."""
+    scene, A = _setup(renderer, name)
     S = A.oracle_struct()
     n = 64 * 48 * 20
     data = np.zeros((n, 12), np.float32)
     po.port().oracle_generate(C.byref(S), data.reshape(-1), 20, 0, n, 0)
-    rays = np.ascontiguousarray(data[:, :6])
-    prim, t = renderer.trace_closest(rays, with_spheres=True)
-    assert (prim[(prim >= 0)] < len(A.spheres) + len(A.triangles)).all()
-    assert ((prim >= 0) & (prim < len(A.spheres))).sum() > 100  # both spheres are in view
+    seeds = (np.arange(n, dtype=np.uint64) * 4137874753 + 279220567 * 7).astype(np.uint32)
+    bounced = data.copy()
+    po.port().oracle_process(C.byref(S), bounced.reshape(-1), seeds, n)  # bounce-1 rays: origins on spheres / walls
+    alive = ~(bounced[:, 6:9] == 0).all(axis=1)
+    batches = {"primary": np.ascontiguousarray(data[:, :6]), "bounce1": np.ascontiguousarray(bounced[alive][:, :6]),
+               "random": scene_rays(A, 50_000, seed=17)}
+    ns = len(A.spheres)
+    sphere_hits = 0
+    for tag, rays in batches.items():
+        prim, t = renderer.trace_closest(rays, with_spheres=True)
+        want_prim, want_t, _ = oracle_closest(A, rays, near_first=True, with_spheres=True)
+        # distance to the centre of the sphere that was hit: scale of the cancellation in b -+ sqrt(disc)
+        cen = A.spheres[np.clip(want_prim, 0, max(ns - 1, 0)), :3] if ns else np.zeros((len(rays), 3), np.float32)
+        b_scale = np.where((want_prim >= 0) & (want_prim < ns), np.linalg.norm(cen - rays[:, :3], axis=1), 0.0)
+        diff = np.abs(t.astype(np.float64) - want_t.astype(np.float64))
+        tol = 1e-5 * np.maximum(np.abs(t), np.abs(want_t)) + 2.4e-7 * b_scale + 1e-6 * scene_diag(A) * (len(A.triangles) > 0)
+        both_miss = (prim < 0) & (want_prim < 0)
+        bad = ~(both_miss | (diff <= tol))
+        assert bad.sum() == 0, f"{name}/{tag}: {bad.sum()} mismatches, first {np.nonzero(bad)[0][:5]}"
+        assert ((prim != want_prim) & ~both_miss).sum() <= 5, f"{name}/{tag}: primitive flips inside the tie tolerance"
+        sphere_hits += int(((prim >= 0) & (prim < ns)).sum())
+    assert sphere_hits > 1000
+
+
+# test_process_step_vs_oracle: (out-of-tolerance fraction, dead/alive flip fraction) allowed per scene = 2 x the worst value
+# measured over the three bounces on B200 (printed by the test; table in profiles/r2_parity_fractions.md)
+PROCESS_STEP_BOUNDS = {"cornell": (5e-3, 2e-3), "cornell_plus": (5e-3, 2e-3), "spheres": (5e-3, 2e-3), "teapot": (5e-3, 2e-3),
+                       "glass_teapot": (5e-3, 2e-3), "lamp": (5e-3, 2e-3)}
+PROCESS_STEP_MEASURED = {}
 
 
 @pytest.mark.parametrize("name", ALL_SCENES)
@@ -129,11 +161,16 @@ def test_process_step_vs_oracle(renderer, name):
         got = renderer.process_rays(data, seeds)
         scale = np.maximum(np.abs(want), 1.0)
         rec_ok = (np.abs(got - want) <= 2e-4 * scale).all(axis=1) | ~np.isfinite(want).all(axis=1)
-        frac = rec_ok.mean()
-        assert frac >= 0.995, f"{name} bounce {bounce}: only {frac:.4%} of records within tolerance"
+        miss_frac = 1.0 - rec_ok.mean()
         dead_w = (want[:, 6:9] == 0).all(axis=1)
         dead_g = (got[:, 6:9] == 0).all(axis=1)
-        assert (dead_w != dead_g).mean() < 2e-3
+        flip_frac = (dead_w != dead_g).mean()
+        print(f"process_step {name} bounce {bounce}: out-of-tolerance records {miss_frac:.3e}, dead/alive flips {flip_frac:.3e}")
+        PROCESS_STEP_MEASURED[name, bounce] = (miss_frac, flip_frac)
+        # bounds = 2 x the worst fraction measured on B200 (profiles/r2_parity_fractions.md), floor of 2 records
+        bound_miss, bound_flip = PROCESS_STEP_BOUNDS[name]
+        assert miss_frac <= max(bound_miss, 2.0 / n), f"{name} bounce {bounce}: {miss_frac:.3e} of the records out of tolerance (bound {bound_miss:.1e})"
+        assert flip_frac <= max(bound_flip, 2.0 / n), f"{name} bounce {bounce}: {flip_frac:.3e} dead/alive flips (bound {bound_flip:.1e})"
         data = want  # continue from the oracle's state so errors do not compound
 
 
@@ -251,6 +288,85 @@ def test_spatial_split_tree_same_hits_and_image(renderer, name):
     assert abs(n1 - n0) <= max(2, 1e-5 * n0)
     rel_rmse = float(np.sqrt(np.mean((img1 - img0) ** 2)) / np.sqrt(np.mean(img0 ** 2)))
     assert rel_rmse < 5e-3 and abs(float(img1.mean()) / float(img0.mean()) - 1.0) < 1e-3
+
+
+@pytest.mark.parametrize("nodes", ["q16", "w4"])
+@pytest.mark.parametrize("name", ALL_SCENES)
+def test_compressed_node_formats_same_hits(renderer, name, nodes):
+    """the tracer on 32-byte quantised records (q16) and on 4-wide quantised nodes (w4). Boxes only grow and
+    hits come from the same exact triangle test, so every ray's hit distance is BIT-identical to the float-box walk and the
+    primitive differs only where two triangles are hit at exactly the same distance (visiting order) - so the oracle and
+    reference-kernel bars the float-box walk is held to carry over; a render has the same live-ray counters (integers)."""
+    scene, A = _setup(renderer, name, 96, 64, 40, 6)
+    rays = scene_rays(A, 200_000, seed=13)
+    prim0, t0 = renderer.trace_closest(rays, with_spheres=True, stats=True)
+    visits0 = renderer.last_stats.internal_visits
+    img0 = renderer.render(sort=False)
+    live0 = tuple(renderer.last_stats.live_per_bounce[:6])
+    r = rt.Renderer(0, nodes=nodes)
+    try:
+        r.upload(scene)
+        assert r.node_mode == nodes
+        prim1, t1 = r.trace_closest(rays, with_spheres=True, stats=True)
+        visits1 = r.last_stats.internal_visits
+        assert t1.tobytes() == t0.tobytes()
+        flips = prim1 != prim0
+        assert flips.sum() <= 20 and (t1[flips] == t0[flips]).all()
+        if nodes == "q16" and visits0 > 0:  # same tree, slightly larger boxes: a few per cent more visited records at most
+            assert visits0 <= visits1 <= 1.08 * visits0, (visits0, visits1)
+        img1 = r.render(sort=False)
+        assert tuple(r.last_stats.live_per_bounce[:6]) == live0
+        assert np.allclose(img1, img0, rtol=1e-4, atol=1e-4 * max(img0.mean(), 1e-6))
+    finally:
+        r.close()
+
+
+def test_compressed_nodes_on_device_built_tree_and_no_bvh():
+    """q16 / w4 derive from the packed records whatever produced them: the device BVH build, or `no_bvh`'s chains."""
+    for use_bvh, name, n in (("device", "teapot", 100_000), (False, "cornell", 20_000)):
+        scene = rt.load_scene(name + ".scene", use_bvh=use_bvh, cwd=SCENES).set_image(64, 48, 20, 4, 1.0)
+        out = {}
+        for nodes in ("f32", "q16", "w4"):
+            r = rt.Renderer(0, nodes=nodes)
+            try:
+                r.upload(scene)
+                if nodes == "f32":
+                    rays = scene_rays(oracle_arrays(load(name)), n, seed=3)
+                out[nodes] = r.trace_closest(rays)
+            finally:
+                r.close()
+        for nodes in ("q16", "w4"):
+            assert out[nodes][1].tobytes() == out["f32"][1].tobytes()
+            assert (out[nodes][0] != out["f32"][0]).sum() <= 5
+
+
+def test_ray_ranges_sum_to_the_whole_frame(renderer):
+    """The per-GPU split for pass counts that do not divide (BASELINE configs[3]: teapot, 50 passes on 8 GPUs): a frame
+    rendered as 8 UNEQUAL ranges of its ray sequence (rt_render_opts.ray_first / ray_count; ranges cut passes anywhere,
+    also inside a pixel's samples) sums to the whole frame, with exactly equal live-ray counters per bounce."""
+    w, h, spp, bounces = 64, 48, 70, 8  # 4 passes: 20, 20, 20, 10 samples
+    _setup(renderer, "cornell_plus", w, h, spp, bounces)
+    whole = renderer.render(sort=False)
+    st = renderer.last_stats
+    live = np.array(st.live_per_bounce[:bounces], np.int64)
+    total = w * h * spp
+    assert st.primary_rays == total
+    cuts = [0, 1, 977, w * h * 20 - 3, w * h * 20 + 5, w * h * 47, w * h * 60, w * h * 60 + 1234, total]
+    acc = np.zeros_like(whole, dtype=np.float64)
+    live_sum = np.zeros(bounces, np.int64)
+    primaries = 0
+    for sort, (a, b) in zip((False, True) * 4, zip(cuts[:-1], cuts[1:])):
+        acc += renderer.render(sort=sort, ray_first=a, ray_count=b - a)
+        live_sum += np.array(renderer.last_stats.live_per_bounce[:bounces], np.int64)
+        primaries += renderer.last_stats.primary_rays
+    assert primaries == total
+    assert (live_sum == live).all()
+    assert np.allclose(acc, whole, rtol=1e-4, atol=1e-4 * whole.mean())
+    # a range past the end is clipped; an empty range renders nothing
+    img = renderer.render(sort=False, ray_first=total - 10, ray_count=1000)
+    assert renderer.last_stats.primary_rays == 10
+    img = renderer.render(sort=False, ray_first=total + 5, ray_count=7)
+    assert renderer.last_stats.primary_rays == 0 and not img.any()
 
 
 def test_bounce_limit_is_reported(renderer):

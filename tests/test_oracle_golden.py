@@ -104,6 +104,40 @@ def test_generate_and_process_golden(name):
         assert same.all(), f"{name} bounce {b}: {np.count_nonzero(~same.all(axis=1))} records differ"
 
 
+@pytest.mark.parametrize("name", ["spheres", "cornell_plus", "cornell"])
+def test_sphere_leg_against_golden_process_records(name):
+    """oracle_closest_hit_ex(with_spheres=1) = process_ray's sphere loop (scene.cu:338-372) + the BVH. The reference has no
+    separate function for it, so it is pinned through the reference's own process_ray records in tests/golden: for every
+    ray of bounce 0, 1 and 2 the golden next origin is origin + t * dir (scene.cu:397) bit for bit when the oracle reports
+    a hit, and the golden ray is dead (transmitted = 0, origin unchanged) exactly when it reports a miss. spheres.scene
+    holds the radius-40000 spheres at distance 4e5 (FP32 cancellation), cornell_plus rays that start ON its spheres."""
+    scene = load(name).set_image(32, 24, 25, 6, 1.0)
+    A = oracle_arrays(scene)
+    m = 2048
+    state = G[f"gen_{name}"]
+    sphere_hits = 0
+    for b in range(3):
+        nxt = G[f"proc_{name}_b{b}"]
+        live = ~(state[:, 6:9] == 0).all(axis=1)
+        rays = np.ascontiguousarray(state[:, :6])
+        idx, t, _ = oracle_closest(A, rays, near_first=False, with_spheres=True)
+        idx_n, t_n, _ = oracle_closest(A, rays, near_first=True, with_spheres=True)
+        assert t_n.tobytes() == t.tobytes() and (idx_n != idx).sum() <= 2
+        hit = live & (idx >= 0)
+        miss = live & (idx < 0)
+        with np.errstate(over="ignore", invalid="ignore"):
+            want_origin = (state[:, 0:3] + t[:, None] * state[:, 3:6]).astype(np.float32)
+        assert (want_origin[hit].view(np.uint32) == nxt[hit, 0:3].view(np.uint32)).all(), f"{name} bounce {b}"
+        assert (nxt[miss, 6:9] == 0).all() and (nxt[miss, 0:3].view(np.uint32) == state[miss, 0:3].view(np.uint32)).all()
+        if len(A.spheres) == 0:
+            idx0, t0, _ = oracle_closest(A, rays, near_first=False)
+            assert t0.tobytes() == t.tobytes() and (idx0 == idx).all()
+        sphere_hits += int((hit & (idx < len(A.spheres))).sum())
+        state = nxt
+    if len(A.spheres):
+        assert sphere_hits > 50  # the golden rays are the first 2048 of a pass (top rows): few reach the spheres of cornell_plus
+
+
 @pytest.mark.parametrize("name", ALL_SCENES)
 @pytest.mark.parametrize("mode", [0, 1])
 def test_render_loop_golden(name, mode):

@@ -46,13 +46,15 @@ def scene_rays(arrays, n, seed):
     return np.ascontiguousarray(np.concatenate([o, d], 1), np.float32)
 
 
-def oracle_closest(arrays, rays, near_first):
+def oracle_closest(arrays, rays, near_first, with_spheres=False):
+    """Closest hit per ray from the oracle: the BVH alone (Scene::bvh_closest_hit_distance), or preceded by process_ray's
+    sphere loop (with_spheres)."""
     S = arrays.oracle_struct()
     n = len(rays)
     t = np.zeros(n, np.float32)
     idx = np.zeros(n, np.int32)
     c = po.Counters()
-    po.port().oracle_closest_hit(C.byref(S), rays, n, 1 if near_first else 0, t, idx, C.byref(c))
+    po.port().oracle_closest_hit_ex(C.byref(S), rays, n, 1 if near_first else 0, 1 if with_spheres else 0, t, idx, C.byref(c))
     return idx, t, c
 
 
