@@ -1,18 +1,21 @@
 #!/usr/bin/env python3
 """bench.py — headline metric of the render path: Mrays/s (all bounces) on lamp.scene, ms/frame.
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload lamp_4k|lamp_1k|...] [--impl reference]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload lamp_4k|teapot_1k|...] [--impl reference]
   torchrun ... bench.py --gpus N ...        (one rank per GPU, NCCL; launched by the driver for N > 1)
 
 A "step" is one whole frame of the workload: every pass of every bounce (generate -> closest hit -> shade -> compact
-[-> reorder]) plus, for N > 1, the NCCL reduce of the float accumulation buffer to rank 0. The frame's passes are split
-across the ranks (strong scaling: the frame is fixed). `value` = live ray-bounces of the whole frame /
-device time (CUDA events on the render stream, max over ranks). `e2e` is the same frame through the reference-facing
-call with HOST buffers: rt_scene_upload (BVH packing + H2D) + render + D2H of the sums, every step.
+[-> reorder]) plus, for N > 1, the NCCL reduce of the float accumulation buffer to rank 0. The frame's RAY SEQUENCE is
+split into equal contiguous shares across the ranks (rt_render_opts.ray_first / ray_count: whole passes when the pass
+count divides, partial passes otherwise; strong scaling: the frame is fixed). `value` = live ray-bounces
+of the whole frame / device time (CUDA events on the render stream, max over ranks). `e2e` is the same frame through the
+reference-facing call with HOST buffers: rt_scene_upload (H2D of the scene) + render + D2H of the sums, every step.
 
-Only the `cpu_baseline` leg and `--impl reference` execute anything under oracle/ (the reference's own CPU path).
+Only the `cpu_baseline` leg and `--impl reference` execute anything under oracle/ (the reference's own CPU path); the
+reference arm loads nothing of the product.
 """
 import argparse
+import glob
 import json
 import os
 import re
@@ -31,7 +34,7 @@ REF_BIN = os.path.join(ROOT, "oracle", "_ref", "raytracing_ref")
 WORKLOADS = {
     "lamp_4k": ("lamp", 3840, 2160, 640, 10),      # BASELINE.json configs[4]: "lamp.scene at 4K and high rays_per_pixel"
     "lamp_1k": ("lamp", 1000, 1000, 1000, 10),     # lamp.scene as shipped
-    "teapot_1k": ("teapot", 1000, 1000, 1000, 10),
+    "teapot_1k": ("teapot", 1000, 1000, 1000, 10),  # BASELINE.json configs[3]: teapot.scene as shipped, 1/2/4/8 GPUs
     "cornell_1k": ("cornell", 1000, 1000, 1000, 10),
     "cornell_plus_1k": ("cornell_plus", 1000, 1000, 1000, 10),
     "spheres_1k": ("spheres", 1000, 1000, 1000, 10),
@@ -49,10 +52,23 @@ def parse_args():
     p.add_argument("--workload", default="lamp_4k", choices=sorted(WORKLOADS))
     p.add_argument("--impl", default="b200", choices=["b200", "reference"])
     p.add_argument("--sort", type=int, default=0, help="1 = reorder live rays between bounces")
+    p.add_argument("--nodes", default=None, choices=["f32", "q16", "w4"], help="node format of the tracer (default: the library's)")
     p.add_argument("--pass-group", type=int, default=0, help="passes traced together as one wave; 0 = auto, 1 = one pass per wave")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-ref-gpu", action="store_true", help="skip timing the reference's sm_100a GPU binary")
+    p.add_argument("--no-extras", action="store_true", help="skip the extra keys (device BVH build, spatial-split tree)")
     return p.parse_args()
+
+
+def config_for(args):
+    """The `config` object of the JSON line: the same keys and values in both arms (the driver compares them)."""
+    scene, w, h, spp, bounces = WORKLOADS[args.workload]
+    note = {"lamp": " (lamp-subset geometry: 48 of the 50 meshes are in the checkout)", "teapot": " (synthetic env map: the asset is not in the checkout)",
+            "glass_teapot": " (synthetic env map: the asset is not in the checkout)"}.get(scene, "")
+    return {"workload": f"{scene}.scene {w}x{h} {spp} spp {bounces} bounces{note}",
+            "passes": (spp + PASS_SPP - 1) // PASS_SPP, "pass_spp": PASS_SPP, "sort": int(bool(args.sort)),
+            "parallelism": f"ray-sequence split x{args.gpus} + NCCL reduce",
+            "l2": "inputs larger than L2: ray queues are %.1f GB per pass; the packed scene is L2-resident by nature" % (w * h * PASS_SPP * 40 * 2 / 1e9)}
 
 
 class ClockSampler:
@@ -104,9 +120,6 @@ def visible_gpu_index(local_rank):
     return local_rank
 
 
-from cuda_raytracer_b200.multi_gpu import DeviceFramebuffer as _DevBuf, pass_range  # noqa: E402  (host-side split logic, tested on CPU with gloo)
-
-
 # ---- reference arm / cpu_baseline: the reference's own CPU path (oracle/_ref/raytracing_ref cpu no_gpu) -------------
 def _scene_file_with_image(scene, w, h, spp, bounces):
     src = open(os.path.join(SCENES, scene + ".scene")).read()
@@ -118,35 +131,49 @@ def _scene_file_with_image(scene, w, h, spp, bounces):
     return f.name
 
 
+def host_threads():
+    """Threads the reference's OpenMP loops get: every core this process may run on."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def ref_env():
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to its workers; the reference's CPU path is an OpenMP program and is
+    given every host core explicitly."""
+    env = dict(os.environ)
+    env["OMP_NUM_THREADS"] = str(host_threads())
+    env.pop("OMP_PROC_BIND", None)
+    return env
+
+
 def live_per_primary(scene, w, h, bounces):
-    """Live ray-bounces per primary ray, counted by the oracle port on a 1/8-scale image of the same camera (CPU seeds).
-    The reference binary prints no counts; the ratio converts its `CPU Took` time into the metric's unit."""
+    """Live ray-bounces per primary ray of the reference's CPU path, counted by the reference's OWN functions (load_scene,
+    generate_initial_rays, process_ray behind oracle/_ref/libref_shim.so, CPU seeds) on a 1/8-scale image of the same
+    camera. The reference binary prints no counts; the ratio converts its `CPU Took` time into the metric's unit."""
     import ctypes as C
 
     import numpy as np
 
+    os.environ["OMP_NUM_THREADS"] = str(host_threads())  # before libgomp starts (the shim's loops are OpenMP too)
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import pyoracle as po
 
-    import cuda_raytracer_b200 as rt
-    s = rt.load_scene(scene + ".scene", cwd=SCENES).set_image(max(16, w // 8), max(16, h // 8), 20, bounces)
-    a = s.arrays()
-    floats = {k: a[k] for k in ("camera_position", "forward", "up", "vertical_fov", "exposure", "min_coord", "inv_dimensions",
-                                "scaled_right", "scaled_up", "near_plane_top_left", "inv_width", "inv_height")}
-    arrays = po.SceneArrays(a["spheres"], a["triangles"], a["material_indices"], a["materials"], a["bvh"], a["env"], a["env_w"],
-                            a["env_h"], (a["width"], a["height"], a["ray_count"], a["bounces"]), floats)
-    S = arrays.oracle_struct()
-    img = np.zeros(a["width"] * a["height"] * 3, np.float32)
-    c = po.Counters()
-    po.port().oracle_render(C.byref(S), 0, 0, -1, img, C.byref(c))
-    return c.live_ray_bounces / float(a["width"] * a["height"] * 20), po.port().oracle_max_threads()
+    ref = po.RefScene(scene + ".scene", cwd=SCENES)
+    sw, sh = max(16, w // 8), max(16, h // 8)
+    ref.set_image(sw, sh, 20, bounces, 1.0)
+    img = np.zeros(sw * sh * 3, np.float32)
+    live = C.c_longlong()
+    po.shim().ref_render(ref.handle, 0, img, C.byref(live))
+    return live.value / float(sw * sh * 20)
 
 
 def run_reference_cpu(scene, w, h, spp, bounces):
     """One run of the reference program's CPU path; returns seconds from its own `CPU Took` line."""
     path = _scene_file_with_image(scene, w, h, spp, bounces)
     try:
-        out = subprocess.run([REF_BIN, path, "cpu", "no_gpu"], cwd=SCENES, capture_output=True, text=True, timeout=1800).stdout
+        out = subprocess.run([REF_BIN, path, "cpu", "no_gpu"], cwd=SCENES, capture_output=True, text=True, timeout=1800, env=ref_env()).stdout
     finally:
         os.unlink(path)
     m = re.search(r"CPU Took ([0-9.eE+-]+)s", out)
@@ -168,11 +195,11 @@ def reference_arm(args, rank, world, emit):
     if rank != 0:
         return 0
     scene, w, h, spp, bounces = WORKLOADS[args.workload]
-    cfg = {"workload": f"{scene}.scene {w}x{h} {spp} spp {bounces} bounces (lamp-subset geometry, synthetic env map)", "l2": "n/a (CPU)"}
     if not os.path.exists(REF_BIN):
         emit({"impl": "reference", "unavailable": "oracle/_ref/raytracing_ref was not built (needs /root/reference at build time)"})
         return 0
-    ratio, threads = live_per_primary(scene, w, h, bounces)
+    ratio = live_per_primary(scene, w, h, bounces)
+    threads = host_threads()
     s_spp = size_cpu_sample(scene, w, h, bounces, 10.0)
     times = []
     for i in range(args.warmup + args.steps):
@@ -182,11 +209,12 @@ def reference_arm(args, rank, world, emit):
     sec = sum(times) / len(times)
     live = ratio * w * h * s_spp
     value = live / sec * 1e-6
-    sample = f"{w}x{h} x {s_spp} spp (one pass of the workload's {spp} spp), `raytracing_ref <scene> cpu no_gpu`, OpenMP {threads} threads"
+    sample = (f"{w}x{h} x {s_spp} spp (one pass of the workload's {spp} spp), `raytracing_ref <scene> cpu no_gpu`, OMP_NUM_THREADS={threads} "
+              f"(nproc {os.cpu_count()}), {ratio:.3f} live ray-bounces per primary ray counted by the reference's own process_ray")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic", "config": cfg,
-            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "kind": "reference", "sample": sample},
+            "dtype": "f32", "data": "synthetic", "config": config_for(args),
+            "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": threads, "nproc": os.cpu_count(), "kind": "reference", "sample": sample},
             "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)
@@ -194,31 +222,59 @@ def reference_arm(args, rank, world, emit):
 
 
 # ---- the B200 arm ------------------------------------------------------------------------------------------------------
-def ref_gpu_timing(scene, w, h, bounces):
-    """The reference's sm_100a GPU build on the same box. Its `GPU Took` timer includes allocation, scene upload and the
-    download, so the steady-state rate is the SLOPE between two spp values (whole passes of 20); the first run of each
-    mode is a discarded warm-up (cold CUDA context / page cache), and the points are far apart so that run-to-run noise
-    (~0.05 s) is small against the difference; every point is the best of two runs."""
-    lo, hi = (100, 500) if w * h <= 1_000_000 else (40, 200)
-    out = {lo: {}, hi: {}}
-    paths = {spp: _scene_file_with_image(scene, w, h, spp, bounces) for spp in (lo, hi)}
+def ref_gpu_timing(scene, w, h, bounces, lpp):
+    """The reference's sm_100a GPU build on the same box (north_star's comparison target). Its `GPU Took` timer
+    (raytracing.cu:172,279-281) includes ~13 cudaMalloc / cudaFree, the pageable scene upload and the download, which do not
+    depend on the sample count; the steady-state rate is therefore the least-squares SLOPE of `GPU Took` over five sample
+    counts (whole passes of 20), every point the best of three runs after one discarded warm-up run per mode. Reported with
+    the standard error of the slope (`spread`) and the largest residual, so that a noisy box shows."""
+    pts = (100, 200, 300, 400, 500) if w * h <= 1_000_000 else (20, 40, 60, 80, 100)
+    paths = {spp: _scene_file_with_image(scene, w, h, spp, bounces) for spp in pts}
 
     def took(spp, flags):
         o = subprocess.run([REF_BIN, paths[spp], *flags], cwd=SCENES, capture_output=True, text=True, timeout=1800).stdout
         m = re.search(r"GPU Took ([0-9.eE+-]+)s", o)
         return float(m.group(1)) if m else None
 
+    out = {"config": f"{scene}.scene {w}x{h}, `GPU Took` at {list(pts)} spp, best of 3 per point, least-squares slope = steady state"}
     try:
         for flags in ((), ("no_sort",)):
             mode = "no_sort" if flags else "sort"
-            took(lo, flags)  # warm-up, discarded
-            for spp in (lo, hi):  # best of two: the reference's timer includes ~13 cudaMalloc/cudaFree, which jitter
-                a, b = took(spp, flags), took(spp, flags)
-                out[spp][mode] = min(a, b) if a and b else (a or b)
+            took(pts[0], flags)  # warm-up, discarded
+            ys = []
+            for spp in pts:
+                runs = [t for t in (took(spp, flags) for _ in range(3)) if t]
+                ys.append(min(runs) if runs else None)
+            if any(y is None for y in ys):
+                out[mode] = {"unavailable": "no `GPU Took` line"}
+                continue
+            n = len(pts)
+            mx, my = sum(pts) / n, sum(ys) / n
+            sxx = sum((x - mx) ** 2 for x in pts)
+            slope = sum((x - mx) * (y - my) for x, y in zip(pts, ys)) / sxx
+            icpt = my - slope * mx
+            res = [y - (icpt + slope * x) for x, y in zip(pts, ys)]
+            se = (sum(r * r for r in res) / max(1, n - 2) / sxx) ** 0.5
+            rate = lpp * w * h / max(slope, 1e-12) * 1e-6
+            out[mode] = {"value": rate, "unit": "Mrays/s", "spread": rate * se / max(slope, 1e-12), "spread_rel": se / max(slope, 1e-12),
+                         "s_per_spp": slope, "fixed_cost_s": icpt, "max_residual_s": max(abs(r) for r in res), "gpu_took_s": dict(zip(pts, ys))}
     finally:
         for pth in paths.values():
             os.unlink(pth)
     return out
+
+
+def newest_ncu_summary():
+    """profiles/r*_traffic.json with the highest name (= the latest capture). None if there is none."""
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))
+    for f in reversed(files):
+        try:
+            d = json.load(open(f))
+            d["_file"] = os.path.relpath(f, ROOT)
+            return d
+        except (OSError, ValueError):
+            continue
+    return None
 
 
 def main():
@@ -243,6 +299,8 @@ def main():
     import torch
 
     import cuda_raytracer_b200 as rt
+    from cuda_raytracer_b200.core import build_id
+    from cuda_raytracer_b200.multi_gpu import DeviceFramebuffer as _DevBuf, ray_range
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the render core has no CPU fallback (use --impl reference for the CPU path)")
@@ -255,10 +313,12 @@ def main():
     scene_name, w, h, spp, bounces = WORKLOADS[args.workload]
     scene = rt.load_scene(scene_name + ".scene", cwd=SCENES).set_image(w, h, spp, bounces)
     total_passes = (spp + PASS_SPP - 1) // PASS_SPP
-    first, count = pass_range(total_passes, rank, world)
+    total_rays = w * h * spp
+    first, count = ray_range(total_rays, rank, world)
+    share = dict(ray_first=first, ray_count=count) if world > 1 else {}  # one GPU: the whole frame, no range
     sort = bool(args.sort)
 
-    r = rt.Renderer(local_rank)
+    r = rt.Renderer(local_rank, nodes=args.nodes)
     r.upload(scene)
     n_floats = w * h * 3
     host_out = torch.empty(n_floats, dtype=torch.float32).pin_memory().numpy()
@@ -268,42 +328,40 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def frame(timing=False):
-        """One step, inputs resident: this rank's passes, then the reduce of the accumulation buffer to rank 0."""
-        if count > 0:
-            ptr = r.render_device(sort=sort, pass_first=first, pass_count=count, timing=timing, pass_group=args.pass_group)
+    def frame(timing=False, keep=None):
+        """One step, inputs resident: this rank's share of the rays, then the reduce of the accumulation buffer to rank 0."""
+        if count > 0 or world == 1:
+            ptr = r.render_device(sort=sort, timing=timing, pass_group=args.pass_group, **share)
             st = r.last_stats
             dev_s, live, launches, tr_ms, sh_ms, so_ms = st.loop_seconds, st.live_ray_bounces, st.kernel_launches, st.trace_ms, st.shade_ms, st.sort_ms
-        else:  # more ranks than passes: contribute zeros
-            ptr = r.render_device(sort=sort, pass_first=0, pass_count=1)
+        else:  # more ranks than rays: contribute zeros
+            ptr = r.render_device(sort=sort, ray_first=total_rays, ray_count=1)
             dev_s = live = launches = tr_ms = sh_ms = so_ms = 0
         red_s = 0.0
         if dist is not None:
             fb = torch.as_tensor(_DevBuf(ptr, n_floats), device=f"cuda:{local_rank}")
-            if count == 0:
-                fb.zero_()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
             dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)
             e1.record()
-            e1.synchronize()
+            e1.synchronize()  # the core's next render writes this buffer on its own stream: the reduce must be over
             red_s = e0.elapsed_time(e1) * 1e-3
+            if keep is not None and rank == 0:
+                keep.append(fb.clone())
         return dev_s + red_s, live, launches, tr_ms, so_ms, red_s, sh_ms
 
     e2e_upload = []
 
     def frame_e2e():
-        """The reference-facing call with host buffers: upload (BVH packing + H2D), render, D2H of the sums."""
+        """The reference-facing call with host buffers: upload (H2D of the scene), render, D2H of the sums."""
         t0 = time.perf_counter()
         r.upload(scene)
         e2e_upload.append(time.perf_counter() - t0)
         if dist is None:
             r.render(sort=sort, out=host_out.reshape(h, w, 3), pass_group=args.pass_group)
         else:
-            ptr = r.render_device(sort=sort, pass_first=first, pass_count=max(count, 1), pass_group=args.pass_group)
+            ptr = r.render_device(sort=sort, pass_group=args.pass_group, **(share if count > 0 else dict(ray_first=total_rays, ray_count=1)))
             fb = torch.as_tensor(_DevBuf(ptr, n_floats), device=f"cuda:{local_rank}")
-            if count == 0:
-                fb.zero_()
             dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
                 torch.from_numpy(host_out).copy_(fb, non_blocking=False)
@@ -321,8 +379,9 @@ def main():
 
     sampler = ClockSampler(visible_gpu_index(local_rank))
     sampler.start()  # nvidia-smi needs ~0.5 s to deliver its first row: start it ahead of the warm-up
-    for _ in range(args.warmup):
-        frame()
+    first_frame = []
+    for i in range(args.warmup):
+        frame(keep=first_frame if i == 0 else None)
     barrier()
     sampler.mark()
     wall0 = time.perf_counter()
@@ -353,6 +412,22 @@ def main():
     barrier()
     e2e_s = sum(e2e_t)
 
+    # N > 1: the reduced frame of the first step against a one-GPU render of the same frame on rank 0 (same pass seeds, so the
+    # images agree up to float summation order) and the summed live-ray counters against that render's
+    image_check = None
+    if dist is not None:
+        live_first = torch.tensor([float(per_step[0][1])], dtype=torch.float64, device="cuda")
+        dist.all_reduce(live_first, op=dist.ReduceOp.SUM)
+        if rank == 0 and first_frame:
+            ptr = r.render_device(sort=sort, pass_group=args.pass_group)
+            one = torch.as_tensor(_DevBuf(ptr, n_floats), device=f"cuda:{local_rank}")
+            got = first_frame[0]
+            rel_rmse = float(torch.sqrt(torch.mean((got - one) ** 2)) / torch.sqrt(torch.mean(one ** 2)))
+            image_check = {"rel_rmse_vs_1gpu": rel_rmse, "live_ray_bounces_n_gpu": int(live_first.item()),
+                           "live_ray_bounces_1gpu": int(r.last_stats.live_ray_bounces),
+                           "ok": bool(rel_rmse <= 1e-4 and int(live_first.item()) == int(r.last_stats.live_ray_bounces))}
+        dist.barrier()
+
     if dist is not None:
         t = torch.tensor([dev_s, e2e_s, tr_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -367,7 +442,7 @@ def main():
 
     a = scene.desc()
     scene_bytes = (a.sphere_count * 16 + a.triangle_count * 48 + (a.sphere_count + a.triangle_count) * 2 + a.material_count * 48 +
-                   (a.bvh_node_count // 2 + 1) * 64 + a.env_width * a.env_height * 16)
+                   a.bvh_node_count * 32 + a.env_width * a.env_height * 12)
     value = live / dev_s * 1e-6
     e2e_value = live / e2e_s * 1e-6
     peaks = {}
@@ -376,61 +451,82 @@ def main():
     except OSError:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    # DRAM traffic of the dominant kernel comes from the committed ncu capture (never measured under the profiler here):
-    # bytes per live ray-bounce x the ray-bounces one average launch of the timed region processed
-    traffic = None
-    try:
-        tr = json.load(open(os.path.join(ROOT, "profiles", "r1k_traffic.json")))
-        n_trace_launches = max(1, sum(p[2] for p in attr_step) // 2)  # every bounce = one trace + one shade launch (sort off)
-        traffic = tr["dram_bytes_per_live_ray_bounce"] * sum(p[1] for p in attr_step) / n_trace_launches
-    except (OSError, KeyError, ValueError):
-        pass
+    l2_peak = r.probe_copy_gbs(16 << 20, 200)  # 2 x 16 MB: resident in the 126 MB L2
     # dominant kernel = trace_rays_kernel: algorithmic bytes of rank 0's launches / their summed CUDA-event durations
     live_rank0 = sum(p[1] for p in attr_step)
-    achieved = live_rank0 * trace_bytes_per_unit / max(1e-9, tr_ms * 1e-3) * 1e-9
+    trace_s, shade_s = max(1e-9, tr_ms * 1e-3), max(1e-9, sh_ms * 1e-3)
+    achieved = live_rank0 * trace_bytes_per_unit / trace_s * 1e-9
+    n_trace_launches = max(1, sum(p[2] for p in attr_step) // 2) if not sort else None  # a bounce = one trace + one shade launch
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "kernel": "trace_rays_kernel", "bytes_per_ray_bounce": trace_bytes_per_unit, "n_int": n_int, "n_tri": n_tri,
+                "whole_bounce_bytes_per_ray_bounce": bytes_per_unit,
+                "whole_step_achieved": sum(p[1] for p in per_step) * bytes_per_unit / max(1e-9, sum(p[0] for p in per_step)) * 1e-9,
+                "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
+                "kernel_share_of_step": tr_ms * 1e-3 / max(1e-9, attr_s),
+                "frac_note": "SURVEY §8(d)'s contract figure: ALGORITHMIC bytes (ray state + every visited BVH record and tested triangle) over the "
+                             "HBM copy peak. The scene is L1/L2-resident, so this fraction exceeds 1 and bounds nothing; the fractions of what each "
+                             "memory level actually carries and the limiter are the keys below",
+                "l2_peak_gbs": l2_peak, "l2_peak_source": "rt_probe_copy_gbs: 2 x 16 MB device copy, read + write, measured in this run",
+                "timing_note": "kernel durations: CUDA event pairs around every launch in %d attribution step(s) run right after the timed region "
+                               "(one wave at a time, %.1f ms per step); the timed region itself runs two waves at a time on two streams, where "
+                               "per-kernel intervals would overlap" % (args.steps, attr_s / args.steps * 1e3)}
+    ncu = newest_ncu_summary()
+    if ncu is not None:
+        same_build = ncu.get("build_id") == build_id()
+        roofline["ncu_source"] = {"file": ncu["_file"], "raw_csv": ncu.get("raw_csv"), "build_id": ncu.get("build_id"), "this_build_id": build_id(),
+                                  "same_build": same_build, "workload": ncu.get("workload")}
+        tk, sk = ncu.get("trace_rays_kernel", {}), ncu.get("shade_kernel", {})
+        if same_build and args.workload == "lamp_4k" and not sort and tk:
+            # per live ray-bounce figures of the capture x this run's ray-bounces / this run's kernel time
+            roofline["traffic"] = tk["dram_bytes_per_live_ray_bounce"] * live_rank0 / n_trace_launches
+            roofline["traffic_note"] = "DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per average trace launch"
+            roofline["dram_frac"] = tk["dram_bytes_per_live_ray_bounce"] * live_rank0 / trace_s * 1e-9 / peak
+            roofline["l2_frac"] = tk["lts_bytes_per_live_ray_bounce"] * live_rank0 / trace_s * 1e-9 / l2_peak
+            for k in ("l1_wavefront_pct", "issue_active", "lanes_per_inst", "l1_hit_pct", "warp_inst_per_live_ray_bounce"):
+                if k in tk:
+                    roofline[k] = tk[k]
+            roofline["limiter"] = ncu.get("limiter")
+            if sk:
+                roofline["shade_kernel"] = {"share_of_step": sh_ms * 1e-3 / max(1e-9, attr_s),
+                                            "dram_frac": sk["dram_bytes_per_live_ray_bounce"] * live_rank0 / shade_s * 1e-9 / peak,
+                                            "l2_frac": sk["lts_bytes_per_live_ray_bounce"] * live_rank0 / shade_s * 1e-9 / l2_peak,
+                                            **{k: sk[k] for k in ("l1_wavefront_pct", "issue_active", "lanes_per_inst") if k in sk}}
+        elif not same_build:
+            roofline["traffic_note"] = "the newest ncu capture under profiles/ is of another build: traffic and the per-level fractions are left out"
     line = {
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{scene_name}.scene {w}x{h} {spp} spp {bounces} bounces (lamp-subset geometry, synthetic env map)",
-                   "passes": total_passes, "pass_spp": PASS_SPP, "pass_group": args.pass_group or "auto (70 % of free memory)", "sort": int(sort), "parallelism": f"spp-split x{world} + NCCL reduce",
-                   "l2": "inputs larger than L2: ray queues are %.1f GB per pass; the packed scene (%.0f MB) is L2-resident by nature"
-                         % (w * h * PASS_SPP * 40 * 2 / 1e9, scene_bytes / 1e6)},
+        "config": config_for(args), "run": {"pass_group": args.pass_group or "auto (70 % of free memory)", "nodes": r.node_mode, "build_id": build_id()},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_s / args.steps * 1e3,
                 "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(n_floats * 4),
                 "ms_each": [round(t * 1e3, 2) for t in e2e_t], "upload_ms_each": [round(t * 1e3, 2) for t in e2e_upload[-len(e2e_t):]]},
         "gpu_launches": int(launches),
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "traffic_note": "DRAM bytes per average trace launch, from profiles/r1k_traffic.json (ncu --set full); algorithmic bytes per such launch = achieved x its duration: the BVH bytes are L1/L2 hits",
-                     "kernel": "trace_rays_kernel", "bytes_per_ray_bounce": trace_bytes_per_unit, "n_int": n_int, "n_tri": n_tri,
-                     "whole_bounce_bytes_per_ray_bounce": bytes_per_unit,
-                     "whole_step_achieved": sum(p[1] for p in per_step) * bytes_per_unit / max(1e-9, sum(p[0] for p in per_step)) * 1e-9,
-                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
-                     "kernel_share_of_step": tr_ms * 1e-3 / max(1e-9, attr_s),
-                     "timing_note": "kernel durations: CUDA event pairs around every launch in %d attribution step(s) run right after the timed region "
-                                    "(one wave at a time, %.1f ms per step); the timed region itself runs two waves at a time on two streams, where "
-                                    "per-kernel intervals would overlap" % (args.steps, attr_s / args.steps * 1e3)},
+        "roofline": roofline,
         "breakdown_ms_per_step": {"trace_kernels": tr_ms / args.steps, "shade_kernels": sh_ms / args.steps, "reorder": so_ms / args.steps, "nccl_reduce": red_s / args.steps * 1e3,
                                   "wall": wall / args.steps * 1e3},
     }
-    if world == 1:  # the same tree built on the device (csrc/device/bvh_build.cuh) vs the host builder
+    if image_check is not None:
+        line["multi_gpu_image_check"] = image_check
+    extras = world == 1 and not args.no_extras
+    if extras:  # the same tree built on the device (csrc/device/bvh_build.cuh) vs the host builder
         dev_scene = rt.load_scene(scene_name + ".scene", use_bvh="device", cwd=SCENES).set_image(w, h, spp, bounces)
         r.upload(dev_scene)
         r.upload(dev_scene)  # second upload: buffers exist, steady state
         line["bvh_build_ms"] = {"host_binned_sah": scene.bvh_build_ms, "device_binned_sah": r.bvh_device_ms,
                                 "triangles": int(a.triangle_count), "nodes": int(a.bvh_node_count)}
         r.upload(scene)
-    if world == 1:  # the same workload on the host tree WITH spatial splits (rt_scene_load(use_bvh = 3)): not the headline, whose
+    if extras:  # the same workload on the host tree WITH spatial splits (rt_scene_load(use_bvh = 3)): not the headline, whose
         # tree is the reference's own; same hits and image, fewer visited records (profiles/r1m_sbvh.md)
         t0 = time.perf_counter()
         sb_scene = rt.load_scene(scene_name + ".scene", use_bvh="sbvh", cwd=SCENES).set_image(w, h, spp, bounces)
         sb_load_s = time.perf_counter() - t0
         r.upload(sb_scene)
-        r.render_device(sort=sort, pass_first=first, pass_count=count, pass_group=args.pass_group)  # warm-up
+        r.render_device(sort=sort, pass_group=args.pass_group)  # warm-up
         sb_s, sb_live = 0.0, 0
         for _ in range(args.steps):
-            r.render_device(sort=sort, pass_first=first, pass_count=count, pass_group=args.pass_group)
+            r.render_device(sort=sort, pass_group=args.pass_group)
             sb_s += r.last_stats.loop_seconds
             sb_live += r.last_stats.live_ray_bounces
         line["sbvh_tree"] = {"value": sb_live / max(sb_s, 1e-9) * 1e-6, "unit": "Mrays/s", "ms_per_step": sb_s / args.steps * 1e3,
@@ -439,22 +535,15 @@ def main():
                              "note": "rt_scene_load(use_bvh = 3): host tree with spatial splits instead of the reference's tree; same core, same image"}
         r.upload(scene)
     if world == 1 and not args.no_cpu_baseline and os.path.exists(REF_BIN):
-        ratio, threads = live_per_primary(scene_name, w, h, bounces)
+        ratio = live_per_primary(scene_name, w, h, bounces)
         s_spp = size_cpu_sample(scene_name, w, h, bounces, 12.0)
         sec = run_reference_cpu(scene_name, w, h, s_spp, bounces)
-        line["cpu_baseline"] = {"value": ratio * w * h * s_spp / sec * 1e-6, "unit": "Mrays/s", "cores": threads, "kind": "reference",
-                                "sample": f"{w}x{h} x {s_spp} spp of the workload, raytracing_ref cpu no_gpu, {sec:.2f} s"}
+        line["cpu_baseline"] = {"value": ratio * w * h * s_spp / sec * 1e-6, "unit": "Mrays/s", "cores": host_threads(), "nproc": os.cpu_count(),
+                                "kind": "reference",
+                                "sample": f"{w}x{h} x {s_spp} spp of the workload, raytracing_ref cpu no_gpu, OMP_NUM_THREADS={host_threads()}, {sec:.2f} s"}
     if world == 1 and not args.no_ref_gpu and os.path.exists(REF_BIN):
-        rw, rh = w, h
-        tg = ref_gpu_timing(scene_name, rw, rh, bounces)
         lpp = live / args.steps / (w * h * spp)
-        lo, hi = sorted(tg)
-        ref = {"config": f"{scene_name}.scene {rw}x{rh}, `GPU Took` at {lo} and {hi} spp (slope = steady state)", "gpu_took_s": tg}
-        for mode in ("sort", "no_sort"):
-            if tg[lo].get(mode) and tg[hi].get(mode):
-                slope = (tg[hi][mode] - tg[lo][mode]) / float(hi - lo)
-                ref[f"{mode}_mrays_per_s_steady"] = lpp * rw * rh / max(slope, 1e-9) * 1e-6
-        line["reference_gpu_sm100a"] = ref
+        line["reference_gpu_sm100a"] = ref_gpu_timing(scene_name, w, h, bounces, lpp)
     emit(line)
     if dist is not None:
         dist.destroy_process_group()

@@ -72,9 +72,12 @@ class Stats(C.Structure):
 
 EXPORTS = [
     # rt_core.h
-    "rt_api_version", "rt_device_count", "rt_create", "rt_set_node_mode", "rt_get_node_mode", "rt_destroy", "rt_last_error", "rt_scene_upload", "rt_scene_set_image",
+    "rt_api_version", "rt_device_count", "rt_host_pin", "rt_host_unpin", "rt_create", "rt_set_node_mode", "rt_get_node_mode", "rt_destroy", "rt_last_error", "rt_scene_upload", "rt_scene_set_image",
     "rt_render", "rt_render_device", "rt_postprocess", "rt_framebuffer_upload", "rt_trace_closest", "rt_generate_rays",
     "rt_process_rays", "rt_sort_pairs", "rt_scene_download_bvh", "rt_scene_bvh_device_ms", "rt_sort_device_ms", "rt_index_divide",
+    "rt_probe_copy_gbs",
+    "rt_multi_create", "rt_multi_destroy", "rt_multi_device_count", "rt_multi_last_error", "rt_multi_context", "rt_multi_set_node_mode",
+    "rt_multi_scene_upload", "rt_multi_render", "rt_multi_reduce_ms", "rt_multi_postprocess",
     # rt_scene.h
     "rt_scene_load", "rt_scene_free", "rt_scene_describe", "rt_scene_set_image_host", "rt_scene_camera_raw",
     "rt_scene_bvh_build_ms", "rt_write_png",
@@ -96,6 +99,9 @@ def lib():
     L.rt_last_error.restype = C.c_char_p
     L.rt_last_error.argtypes = [vp]
     L.rt_create.argtypes = [C.POINTER(vp), C.c_int]
+    L.rt_host_pin.argtypes = [vp, C.c_size_t]
+    L.rt_host_unpin.argtypes = [vp]
+    L.rt_host_unpin.restype = None
     L.rt_set_node_mode.argtypes = [vp, C.c_int]
     L.rt_get_node_mode.argtypes = [vp]
     L.rt_destroy.argtypes = [vp]
@@ -115,8 +121,23 @@ def lib():
     L.rt_scene_bvh_device_ms.restype = C.c_double
     L.rt_sort_device_ms.argtypes = [vp]
     L.rt_sort_device_ms.restype = C.c_double
+    L.rt_probe_copy_gbs.argtypes = [vp, C.c_int64, C.c_int32, C.POINTER(C.c_double)]
     L.rt_index_divide.argtypes = [C.c_uint32, C.c_uint32]
     L.rt_index_divide.restype = C.c_uint32
+    L.rt_multi_create.argtypes = [C.POINTER(vp), C.POINTER(C.c_int), C.c_int]
+    L.rt_multi_destroy.argtypes = [vp]
+    L.rt_multi_destroy.restype = None
+    L.rt_multi_device_count.argtypes = [vp]
+    L.rt_multi_last_error.argtypes = [vp]
+    L.rt_multi_last_error.restype = C.c_char_p
+    L.rt_multi_context.argtypes = [vp, C.c_int]
+    L.rt_multi_context.restype = vp
+    L.rt_multi_set_node_mode.argtypes = [vp, C.c_int]
+    L.rt_multi_scene_upload.argtypes = [vp, C.POINTER(SceneDesc)]
+    L.rt_multi_render.argtypes = [vp, C.POINTER(RenderOpts), vp, C.POINTER(Stats)]
+    L.rt_multi_reduce_ms.argtypes = [vp]
+    L.rt_multi_reduce_ms.restype = C.c_double
+    L.rt_multi_postprocess.argtypes = [vp, C.c_int, vp, vp]
     L.rt_scene_load.argtypes = [C.c_char_p, C.c_int, C.c_int, C.POINTER(vp)]
     L.rt_scene_free.argtypes = [vp]
     L.rt_scene_free.restype = None
@@ -128,6 +149,13 @@ def lib():
     L.rt_write_png.argtypes = [C.c_char_p, C.c_int, C.c_int, vp]
     _lib = L
     return L
+
+
+def build_id():
+    """sha1 of the loaded librtcore.so: ties an ncu capture (profiles/*_traffic.json) to the binary a bench line ran."""
+    import hashlib
+    with open(LIB_PATH, "rb") as f:
+        return hashlib.sha1(f.read()).hexdigest()[:16]
 
 
 def _check(rc, ctx=None):
@@ -347,6 +375,12 @@ class Renderer:
         _check(lib().rt_scene_download_bvh(self._ctx, nodes.ctypes.data, n.value, C.byref(n), order.ctypes.data, triangle_count), self._ctx)
         return nodes, order
 
+    def probe_copy_gbs(self, nbytes, iters=20):
+        """Copy bandwidth (read + write) of a buffer pair of `nbytes` each: L2-resident when small, HBM when large."""
+        g = C.c_double()
+        _check(lib().rt_probe_copy_gbs(self._ctx, int(nbytes), int(iters), C.byref(g)), self._ctx)
+        return g.value
+
     @property
     def bvh_device_ms(self):
         return lib().rt_scene_bvh_device_ms(self._ctx)
@@ -361,6 +395,70 @@ class Renderer:
         assert len(k) == len(v)
         _check(lib().rt_sort_pairs(self._ctx, k.ctypes.data, v.ctypes.data, len(k), bits), self._ctx)
         return k, v
+
+
+class MultiRenderer:
+    """Several GPUs of one box behind one handle (rt_multi): the frame's rays are split across `devices`, the accumulation
+    buffers are summed with one NCCL reduce into devices[0]. Naming one device several times runs the shares on that device
+    (no NCCL)."""
+
+    def __init__(self, devices, nodes=None):
+        devs = (C.c_int * len(devices))(*devices)
+        self._m = C.c_void_p()
+        rc = lib().rt_multi_create(C.byref(self._m), devs, len(devices))
+        if rc != RT_OK:
+            msg = lib().rt_multi_last_error(None)
+            raise RtError(rc, msg.decode() if msg else "")
+        self.devices = list(devices)
+        self.width = self.height = 0
+        self.last_stats = None
+        if nodes is not None:
+            self._check(lib().rt_multi_set_node_mode(self._m, Renderer.NODE_MODES[nodes] if isinstance(nodes, str) else int(nodes)))
+
+    def _check(self, rc):
+        if rc != RT_OK:
+            msg = lib().rt_multi_last_error(self._m)
+            raise RtError(rc, msg.decode() if msg else "")
+
+    def close(self):
+        if self._m:
+            lib().rt_multi_destroy(self._m)
+            self._m = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, scene):
+        d = scene.desc() if isinstance(scene, Scene) else scene
+        self._check(lib().rt_multi_scene_upload(self._m, C.byref(d)))
+        self.width, self.height = d.width, d.height
+        return self
+
+    def render(self, sort=True, out=None, want_host=True, **kw):
+        """rt_multi_render: the combined un-normalised sums (float32[H,W,3]); want_host=False leaves them on devices[0]."""
+        if want_host and out is None:
+            out = np.empty((self.height, self.width, 3), np.float32)
+        o = Renderer._opts(sort, kw.pop("pass_spp", 0), kw.pop("pass_first", 0), kw.pop("pass_count", 0), kw.pop("collect_stats", False),
+                           kw.pop("stream_id", 0), kw.pop("sort_bits", 0), kw.pop("timing", False), kw.pop("pass_group", 0),
+                           kw.pop("root_start", False), kw.pop("single_pipe", False), kw.pop("ray_first", 0), kw.pop("ray_count", 0))
+        assert not kw, f"unknown options {sorted(kw)}"
+        st = Stats()
+        self._check(lib().rt_multi_render(self._m, C.byref(o), out.ctypes.data if want_host else None, C.byref(st)))
+        self.last_stats = st
+        return out if want_host else None
+
+    @property
+    def reduce_ms(self):
+        return lib().rt_multi_reduce_ms(self._m)
+
+    def postprocess(self, bloom=True, want_sum=False, want_rgb8=True):
+        s = np.empty((self.height, self.width, 3), np.float32) if want_sum else None
+        b = np.empty((self.height, self.width, 3), np.uint8) if want_rgb8 else None
+        self._check(lib().rt_multi_postprocess(self._m, 1 if bloom else 0, s.ctypes.data if want_sum else None, b.ctypes.data if want_rgb8 else None))
+        return s, b
 
 
 def device_count():

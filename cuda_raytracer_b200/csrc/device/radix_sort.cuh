@@ -18,8 +18,8 @@
 namespace rtd {
 
 constexpr int kSortBlock = 256;
-constexpr int kSortItems = 16;                          // keys per thread
-constexpr int kSortTile = kSortBlock * kSortItems;      // 4096 keys per tile
+constexpr int kSortItems = 18;                          // keys per thread (RT_SORT_ITEMS selects among the instantiated 12 / 16 / 18; 48 KB of static shared memory caps it)
+constexpr int kSortTile = kSortBlock * 12;              // SMALLEST tile among the variants: sizes the tile-status scratch
 constexpr int kSortWarps = kSortBlock / 32;
 constexpr int kSortMaxPasses = 4;
 constexpr uint32_t kFlagAggregate = 1u << 30;           // tile status: local count published
@@ -74,19 +74,30 @@ __global__ void __launch_bounds__(256) sort_scan_kernel(SortArgs s)
 // One digit pass. values_in == nullptr means "value = element index" (first pass of a fresh permutation).
 // The tile is ranked, re-ordered by digit in shared memory and only then written out, so that consecutive threads
 // store consecutive addresses of a digit's run (a direct scatter writes 32 different sectors per warp instruction).
-__global__ void __launch_bounds__(kSortBlock) sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ values_in,
+//
+// RANK selects how a warp ranks its keys inside a round of 32 (A/B in tools/sort_probe.py, RT_SORT_RANK):
+//   0  match.any; the leader lane reads, bumps and writes back the warp's digit counter (round 1's kernel)
+//   1  match.any; the leader lane bumps the counter with ONE returning shared-memory atomic: no load -> store chain, the 16
+//      rounds only meet in memory (shared atomics of one warp apply in program order; __syncwarp orders the lanes)
+//   2  no match.any: the peer mask of a lane is built from 8 ballots (one per digit bit), counters as in 1. DEFAULT: MATCH.ANY
+//      is the slow instruction of variants 0 / 1 on sm_100a (64 M pairs x 32 bits: 2.58 / 2.55 / 2.32 ms for 0 / 1 / 2 at 18 keys
+//      per thread; CUB's onesweep 2.33 ms; profiles/r2_sort_probe.md)
+// ITEMS = keys per thread (tile = 256 x ITEMS).
+template <int RANK, int ITEMS>
+__global__ void __launch_bounds__(kSortBlock, 3) sort_scatter_kernel(const uint32_t *__restrict__ keys_in, const uint32_t *__restrict__ values_in,
                                                                    uint32_t *__restrict__ keys_out, uint32_t *__restrict__ values_out,
                                                                    SortArgs s, int pass)
 {
+    constexpr int TILE = kSortBlock * ITEMS;
     __shared__ uint32_t warp_hist[kSortWarps][256];  // per-warp digit counts -> exclusive offsets of the warp inside the tile's digit run
-    __shared__ uint32_t digit_base[256];             // global position of the tile's first key of each digit
+    __shared__ uint32_t digit_base[256];             // global position of the tile's first key of each digit MINUS its position in the tile
     __shared__ uint32_t digit_start[256];            // position of that key inside the digit-ordered tile
     __shared__ uint32_t warp_total[kSortWarps];
-    __shared__ uint32_t stage_key[kSortTile], stage_val[kSortTile];
+    __shared__ uint32_t stage_key[TILE], stage_val[TILE];
     __shared__ uint32_t tile_id_sh;
 
     const uint32_t n = *s.count_ptr;
-    const uint32_t num_tiles = (n + kSortTile - 1) / kSortTile;
+    const uint32_t num_tiles = (n + TILE - 1) / TILE;
     if (threadIdx.x == 0) tile_id_sh = atomicAdd(&s.tile_counter[pass], 1u);
     for (int w = 0; w < kSortWarps; w++) warp_hist[w][threadIdx.x] = 0;
     __syncthreads();
@@ -95,32 +106,49 @@ __global__ void __launch_bounds__(kSortBlock) sort_scatter_kernel(const uint32_t
 
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     const uint32_t shift = 8u * pass;
-    const uint32_t tile_base = tile * kSortTile;
-    const uint32_t warp_base = tile_base + warp * (kSortItems * 32u);
-    const uint32_t tile_n = min((uint32_t)kSortTile, n - tile_base);
+    const uint32_t tile_base = tile * TILE;
+    const uint32_t warp_base = tile_base + warp * (ITEMS * 32u);
+    const uint32_t tile_n = min((uint32_t)TILE, n - tile_base);
     const uint32_t lt = (1u << lane) - 1u;
+    const bool full = tile_n == (uint32_t)TILE;
 
-    uint32_t key[kSortItems], val[kSortItems];
-    uint16_t rank[kSortItems];
+    uint32_t key[ITEMS], val[ITEMS];
+    uint16_t rank[ITEMS];
 #pragma unroll
-    for (int r = 0; r < kSortItems; r++) {
+    for (int r = 0; r < ITEMS; r++) {
         uint32_t i = warp_base + r * 32u + lane;
-        bool valid = i < n;
+        bool valid = full || i < n;
         key[r] = valid ? __ldcs(keys_in + i) : 0xFFFFFFFFu;
         val[r] = valid ? (values_in ? __ldcs(values_in + i) : i) : 0u;
     }
-    // stable ranking inside the warp's 512-key segment: rounds in memory order, lanes in order within a round
+    // stable ranking inside the warp's segment: rounds in memory order, lanes in order within a round
+    uint32_t *my_hist = &warp_hist[warp][0];
 #pragma unroll
-    for (int r = 0; r < kSortItems; r++) {
-        uint32_t i = warp_base + r * 32u + lane;
-        bool valid = i < n;
-        uint32_t digit = (key[r] >> shift) & 255u;
-        uint32_t peers = __match_any_sync(0xffffffffu, valid ? digit : (256u + lane));
-        uint32_t leader = __ffs(peers) - 1;
+    for (int r = 0; r < ITEMS; r++) {
+        const uint32_t i = warp_base + r * 32u + lane;
+        const bool valid = full || i < n;
+        const uint32_t digit = (key[r] >> shift) & 255u;
+        uint32_t peers;
+        if (RANK == 2) {
+            peers = full ? 0xffffffffu : __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+            for (int b = 0; b < 8; b++) {
+                const uint32_t m = __ballot_sync(0xffffffffu, (digit >> b) & 1u);
+                peers &= ((digit >> b) & 1u) ? m : ~m;
+            }
+            if (!valid) peers = 1u << lane;
+        } else {
+            peers = __match_any_sync(0xffffffffu, valid ? digit : (256u + lane));
+        }
+        const uint32_t leader = __ffs(peers) - 1;
         uint32_t before = 0;
-        if (valid && lane == leader) {
-            before = warp_hist[warp][digit];
-            warp_hist[warp][digit] = before + __popc(peers);
+        if (RANK == 0) {
+            if (valid && lane == leader) {
+                before = my_hist[digit];
+                my_hist[digit] = before + __popc(peers);
+            }
+        } else {
+            if (valid && lane == leader) before = atomicAdd(&my_hist[digit], (uint32_t)__popc(peers));
         }
         before = __shfl_sync(0xffffffffu, before, leader);
         rank[r] = (uint16_t)(before + __popc(peers & lt));
@@ -143,16 +171,9 @@ __global__ void __launch_bounds__(kSortBlock) sort_scatter_kernel(const uint32_t
         status[dgt] = running | kFlagPrefix;
     } else {
         status[(size_t)tile * 256u + dgt] = running | kFlagAggregate;
-        for (int t = (int)tile - 1; t >= 0; t--) {
-            uint32_t st;
-            do { st = status[(size_t)t * 256u + dgt]; } while ((st & kFlagMask) == 0u);
-            exclusive += st & kValueMask;
-            if (st & kFlagPrefix) break;
-        }
-        status[(size_t)tile * 256u + dgt] = (exclusive + running) | kFlagPrefix;
     }
-    digit_base[dgt] = s.hist[pass * 256 + dgt] + exclusive;
     // exclusive scan of the tile's digit totals over the 256 digits -> start of each digit's run inside the tile
+    // (before the look-back: its latency hides behind the wait for the predecessors)
     uint32_t incl = running;
     for (int off = 1; off < 32; off <<= 1) {
         uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
@@ -162,16 +183,27 @@ __global__ void __launch_bounds__(kSortBlock) sort_scatter_kernel(const uint32_t
     __syncthreads();
     uint32_t before_warps = 0;
     for (uint32_t w = 0; w < warp; w++) before_warps += warp_total[w];
-    digit_start[dgt] = before_warps + incl - running;
+    const uint32_t start = before_warps + incl - running;
+    digit_start[dgt] = start;
+    if (tile != 0) {
+        for (int t = (int)tile - 1; t >= 0; t--) {
+            uint32_t st;
+            do { st = status[(size_t)t * 256u + dgt]; } while ((st & kFlagMask) == 0u);
+            exclusive += st & kValueMask;
+            if (st & kFlagPrefix) break;
+        }
+        status[(size_t)tile * 256u + dgt] = (exclusive + running) | kFlagPrefix;
+    }
+    digit_base[dgt] = s.hist[pass * 256 + dgt] + exclusive - start;
     __syncthreads();
 
     // re-order the tile by digit in shared memory (stable), then stream it out run by run
 #pragma unroll
-    for (int r = 0; r < kSortItems; r++) {
+    for (int r = 0; r < ITEMS; r++) {
         uint32_t i = warp_base + r * 32u + lane;
-        if (i < n) {
+        if (full || i < n) {
             uint32_t digit = (key[r] >> shift) & 255u;
-            uint32_t local = digit_start[digit] + warp_hist[warp][digit] + rank[r];
+            uint32_t local = digit_start[digit] + my_hist[digit] + rank[r];
             stage_key[local] = key[r];
             stage_val[local] = val[r];
         }
@@ -179,8 +211,7 @@ __global__ void __launch_bounds__(kSortBlock) sort_scatter_kernel(const uint32_t
     __syncthreads();
     for (uint32_t j = threadIdx.x; j < tile_n; j += kSortBlock) {
         const uint32_t k = stage_key[j];
-        const uint32_t digit = (k >> shift) & 255u;
-        const uint32_t pos = digit_base[digit] + (j - digit_start[digit]);
+        const uint32_t pos = digit_base[(k >> shift) & 255u] + j;
         keys_out[pos] = k;
         values_out[pos] = stage_val[j];
     }

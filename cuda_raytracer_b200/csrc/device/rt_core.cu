@@ -40,9 +40,8 @@ struct rt_ctx {
     bool has_scene = false;
     DeviceScene ds{};
     void *d_nodes = nullptr, *d_tris = nullptr, *d_materials = nullptr, *d_spheres = nullptr, *d_env = nullptr, *d_matidx = nullptr;
-    size_t cap_nodes = 0, cap_tris = 0, cap_materials = 0, cap_spheres = 0, cap_env = 0, cap_matidx = 0, cap_raw = 0, cap_stage = 0;
+    size_t cap_nodes = 0, cap_tris = 0, cap_materials = 0, cap_spheres = 0, cap_env = 0, cap_matidx = 0, cap_raw = 0;
     void *d_raw = nullptr;    // upload scratch: the caller's raw triangles + texels before the device-side repack
-    void *h_stage = nullptr;  // pinned staging for the packed BVH records
     void *d_build = nullptr;  // device BVH build scratch: nodes, order buffers, level lists, counters
     size_t cap_build = 0;
     int32_t *d_order = nullptr;  // device build: BVH position -> file-order triangle id (inside d_build)
@@ -75,6 +74,7 @@ struct rt_ctx {
     uint32_t trace_batch = kBatch, trace_refill_below = kRefillBelow, trace_node_min = kNodeMin;  // RT_BATCH / RT_REFILL override
     uint32_t *d_keys[2] = {nullptr, nullptr}, *d_vals[2] = {nullptr, nullptr};
     size_t sort_capacity = 0;
+    int sort_rank = 2, sort_items = kSortItems;  // RT_SORT_RANK / RT_SORT_ITEMS: ranking variant and keys per thread of the digit pass
     uint32_t *d_sort_scratch = nullptr;  // hist + tile counters + tile status
     size_t sort_scratch_words = 0;
     PassCounters *d_pc = nullptr;
@@ -127,7 +127,7 @@ static_assert(sizeof(PackedRecord) == 64, "packed record");
 struct Packer {
     const RefNode *nodes;
     std::vector<PackedRecord> out;
-    int max_depth = 0;
+    int max_depth = 0;  // most stack entries a walk can hold = levels of tree records (+ 1 below an oversized leaf's list)
 
     static void set_box(PackedRecord &r, int child, const float *lo, const float *hi)
     {
@@ -152,23 +152,34 @@ struct Packer {
         set_box(r, child, far_away, far_away);
         r.child[child].ref = kEmptyRef;
     }
-    // triangles [begin, end) under box lo/hi -> a leaf ref, or a chain of same-box records when there are > 15
+    // triangles [begin, end) under box lo/hi -> a leaf ref, or, when there are > 15, a LIST of same-box records: child 1 = a
+    // leaf of 15 triangles, child 0 = the rest of the list. Both boxes are equal, so both are hit at the same entry distance and
+    // the tracer (ties go to child 1) tests the leaf first with the rest as the ONE pending stack entry, which it pops before it
+    // goes any deeper: a list of any length needs one stack entry more than its parent (a balanced chain needed log2(n / 15)).
     uint32_t range_ref(int begin, int end, const float *lo, const float *hi, int depth)
     {
         int count = end - begin;
         if (count <= 0) return kEmptyRef;
         if (count <= kMaxLeafTris) return kLeafBit | ((uint32_t)count << kLeafCountShift) | (uint32_t)begin;
         max_depth = std::max(max_depth, depth + 1);
-        size_t idx = out.size();
-        out.emplace_back();
-        int mid = begin + (count + 1) / 2;
-        uint32_t a = range_ref(begin, mid, lo, hi, depth + 1);
-        uint32_t b = range_ref(mid, end, lo, hi, depth + 1);
-        set_box(out[idx], 0, lo, hi);
-        set_box(out[idx], 1, lo, hi);
-        out[idx].child[0].ref = a;
-        out[idx].child[1].ref = b;
-        return (uint32_t)idx;
+        uint32_t head = 0;
+        size_t prev = 0;
+        bool first = true;
+        while (count > kMaxLeafTris) {  // iterative: no_bvh on a large mesh makes lists of 10^4 records
+            const size_t idx = out.size();
+            out.emplace_back();
+            set_box(out[idx], 0, lo, hi);
+            set_box(out[idx], 1, lo, hi);
+            out[idx].child[1].ref = kLeafBit | ((uint32_t)kMaxLeafTris << kLeafCountShift) | (uint32_t)begin;
+            if (first) head = (uint32_t)idx;
+            else out[prev].child[0].ref = (uint32_t)idx;
+            first = false;
+            prev = idx;
+            begin += kMaxLeafTris;
+            count -= kMaxLeafTris;
+        }
+        out[prev].child[0].ref = kLeafBit | ((uint32_t)count << kLeafCountShift) | (uint32_t)begin;
+        return head;
     }
     uint32_t node_ref(int i, int depth)
     {
@@ -205,6 +216,28 @@ struct Packer {
         }
     }
 };
+
+// True when pack_built_nodes_kernel can pack this host tree: root internal; every internal node's children are the adjacent
+// pair (child1 odd, child2 = child1 + 1) allocated AFTER it; every leaf holds 1..15 triangles. *depth = levels of records.
+bool host_tree_packs_on_device(const RefNode *nodes, int count, int *depth)
+{
+    if (count < 3 || !(nodes[0].child2 > nodes[0].child1)) return false;
+    std::vector<uint8_t> level((size_t)count, 0);
+    int deepest = 0;
+    for (int i = 0; i < count; i++) {
+        const RefNode &n = nodes[i];
+        if (n.child2 > n.child1) {
+            if (n.child1 <= i || (n.child1 & 1) == 0 || n.child2 != n.child1 + 1 || n.child2 >= count || level[i] >= 250) return false;
+            level[n.child1] = level[n.child2] = (uint8_t)(level[i] + 1);
+            deepest = std::max(deepest, level[i] + 1);
+        } else {
+            const int tris = n.child1 - n.child2;
+            if (tris < 1 || tris > kMaxLeafTris) return false;
+        }
+    }
+    *depth = deepest;
+    return true;
+}
 
 // Grow-only device buffer: re-uploading a scene of the same size allocates nothing.
 int reserve(rt_ctx *ctx, void **dst, size_t *cap, size_t bytes)
@@ -263,6 +296,9 @@ extern "C" int rt_device_count(void)
 
 extern "C" const char *rt_last_error(const rt_ctx *ctx) { return ctx ? ctx->error.c_str() : rt::global_error(); }
 
+static int init_context(rt_ctx *ctx, int device);
+extern "C" void rt_destroy(rt_ctx *ctx);
+
 extern "C" int rt_create(rt_ctx **out, int device)
 {
     if (!out) return fail(nullptr, RT_ERR_INVALID, "rt_create: null out pointer");
@@ -272,6 +308,17 @@ extern "C" int rt_create(rt_ctx **out, int device)
     if (device < 0 || device >= n) return fail(nullptr, RT_ERR_NO_DEVICE, "rt_create: device index out of range");
     rt_ctx *ctx = new rt_ctx();
     ctx->device = device;
+    const int rc = init_context(ctx, device);
+    if (rc != RT_OK) {  // the message is already in the thread-local slot (rt_last_error(NULL))
+        rt_destroy(ctx);
+        return rc;
+    }
+    *out = ctx;
+    return RT_OK;
+}
+
+static int init_context(rt_ctx *ctx, int device)
+{
     RT_CUDA(ctx, cudaSetDevice(device));
     cudaDeviceProp prop;
     RT_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
@@ -286,6 +333,8 @@ extern "C" int rt_create(rt_ctx **out, int device)
     if (const char *e = std::getenv("RT_TRACE_PER_SM")) ctx->trace_per_sm = std::max(0, std::atoi(e));
     if (const char *e = std::getenv("RT_SHADE_PER_SM")) ctx->shade_per_sm = std::max(0, std::atoi(e));
     if (const char *e = std::getenv("RT_NODES")) ctx->node_mode = std::strcmp(e, "q16") == 0 ? kNodesQ16 : std::strcmp(e, "w4") == 0 ? kNodesW4 : kNodesF32;
+    if (const char *e = std::getenv("RT_SORT_RANK")) ctx->sort_rank = std::min(2, std::max(0, std::atoi(e)));
+    if (const char *e = std::getenv("RT_SORT_ITEMS")) { const int v = std::atoi(e); ctx->sort_items = v <= 12 ? 12 : (v >= 18 ? 18 : 16); }
     if (const char *e = std::getenv("RT_ENTRY_K")) ctx->entry_max = std::min((int)kEntryMax, std::max(0, std::atoi(e)));
     if (const char *e = std::getenv("RT_BATCH")) ctx->trace_batch = (uint32_t)std::min(4096, std::max(4, std::atoi(e)));
     if (const char *e = std::getenv("RT_NODEMIN")) ctx->trace_node_min = (uint32_t)std::min(33, std::max(0, std::atoi(e)));
@@ -294,8 +343,28 @@ extern "C" int rt_create(rt_ctx **out, int device)
     RT_CUDA(ctx, cudaEventCreate(&ctx->ev_stop));
     RT_CUDA(ctx, cudaMalloc(&ctx->d_pc, rt_ctx::kMaxPipes * sizeof(PassCounters)));  // one per pipe
     RT_CUDA(ctx, cudaMalloc(&ctx->d_totals, sizeof(RenderTotals)));
-    *out = ctx;
     return RT_OK;
+}
+
+// Page-lock caller-owned host arrays so that uploads / downloads are true asynchronous DMA at PCIe speed (a pageable copy is
+// staged through the runtime's bounce buffer at ~7 GB/s and blocks the host). The host scene layer pins its own arrays.
+extern "C" int rt_host_pin(const void *ptr, size_t bytes)
+{
+    if (!ptr || bytes == 0) return RT_OK;
+    cudaError_t e = cudaHostRegister(const_cast<void *>(ptr), bytes, cudaHostRegisterPortable | cudaHostRegisterReadOnly);
+    if (e == cudaErrorNotSupported || e == cudaErrorInvalidValue) {  // read-only registration is optional
+        cudaGetLastError();
+        e = cudaHostRegister(const_cast<void *>(ptr), bytes, cudaHostRegisterPortable);
+    }
+    if (e == cudaSuccess || e == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); return RT_OK; }
+    cudaGetLastError();
+    return (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) ? RT_ERR_NO_DEVICE : RT_ERR_CUDA;
+}
+extern "C" void rt_host_unpin(const void *ptr)
+{
+    if (!ptr) return;
+    cudaHostUnregister(const_cast<void *>(ptr));
+    cudaGetLastError();
 }
 
 extern "C" int rt_set_node_mode(rt_ctx *ctx, int mode)
@@ -313,7 +382,7 @@ extern "C" void rt_destroy(rt_ctx *ctx)
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     for (cudaStream_t s : ctx->side) if (s) cudaStreamSynchronize(s);
     release(ctx->d_nodes); release(ctx->d_tris); release(ctx->d_materials); release(ctx->d_spheres); release(ctx->d_env);
-    release(ctx->d_matidx); release(ctx->d_qnodes); release(ctx->d_raw); release(ctx->d_build); if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    release(ctx->d_matidx); release(ctx->d_qnodes); release(ctx->d_raw); release(ctx->d_build);
     release(ctx->d_fb); release(ctx->d_fb_tmp); release(ctx->d_fb_tmp2); release(ctx->d_rgb8);
     for (int i = 0; i < 2; i++) {
         release(ctx->queue[i].qa); release(ctx->queue[i].qb); release(ctx->queue[i].qc);
@@ -483,6 +552,9 @@ extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *s)
         (s->triangle_count + s->sphere_count > 0 && !s->material_indices))
         return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: malformed scene descriptor");
     if ((uint32_t)s->triangle_count > kLeafStartMask) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: more than 2^27 triangles");
+    // the lookup keeps the reference's row stride = map HEIGHT (scene.cu:393): texel index <= (h-1)*h + w-1, inside the
+    // map only when width >= height (the reference's own maps are square; it would read out of bounds otherwise)
+    if (s->env_width < s->env_height) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: environment map must be at least as wide as high (the lookup strides rows by the height, as the reference does)");
     RT_CUDA(ctx, cudaSetDevice(ctx->device));
     ctx->has_scene = false;
     int rc = set_image_block(ctx, s);
@@ -496,6 +568,30 @@ extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *s)
     if (device_build && (rc = build_bvh_on_device(ctx, s, 30)) != RT_OK) return rc;  // MAX_BVH_DEPTH, scene.cu:10
     Packer packer;
     packer.nodes = reinterpret_cast<const RefNode *>(ctx->built_root);
+    if (!device_build) {
+        // A host tree in the reference's own shape (children allocated in adjacent pairs after their parent, leaves of
+        // 1..15 triangles: what generate_bvh produces) is packed into records ON THE DEVICE from its raw 32-byte
+        // nodes: one forward pass on the host validates the shape and finds the depth, nothing else touches the 6 MB.
+        // Anything else (no_bvh's root leaf, oversized leaves, a tree in another order) goes through the host packer.
+        const RefNode *nodes = static_cast<const RefNode *>(s->bvh_nodes);
+        const int count = s->bvh_node_count;
+        int depth = 0;
+        if (host_tree_packs_on_device(nodes, count, &depth)) {
+            if (depth > kStackDepth) return fail(ctx, RT_ERR_INVALID, "rt_scene_upload: BVH deeper than the traversal stack (32)");
+            const int records = (count - 1) / 2;
+            if ((rc = reserve(ctx, &ctx->d_build, &ctx->cap_build, (size_t)count * sizeof(RefNode) + 16)) != RT_OK) return rc;
+            if ((rc = reserve(ctx, &ctx->d_nodes, &ctx->cap_nodes, (size_t)records * 64)) != RT_OK) return rc;
+            int32_t *flag = reinterpret_cast<int32_t *>(static_cast<uint8_t *>(ctx->d_build) + (size_t)count * sizeof(RefNode));
+            RT_CUDA(ctx, cudaMemcpyAsync(ctx->d_build, nodes, (size_t)count * sizeof(RefNode), cudaMemcpyHostToDevice, ctx->stream));
+            pack_built_nodes_kernel<<<(count + 255) / 256, 256, 0, ctx->stream>>>(static_cast<const BuildNode *>(ctx->d_build), count, (float4 *)ctx->d_nodes,
+                                                                                  kLeafBit, kLeafCountShift, kMaxLeafTris, flag);
+            RT_CUDA(ctx, cudaGetLastError());
+            ctx->device_packed = true;
+            ctx->packed_nodes = records;
+            ctx->packed_depth = depth;
+            packer.nodes = nodes;
+        }
+    }
     if (!ctx->device_packed) {
         packer.nodes = device_build ? reinterpret_cast<const RefNode *>(ctx->built_nodes.data()) : static_cast<const RefNode *>(s->bvh_nodes);
         packer.run(device_build ? (int)(ctx->built_nodes.size() / sizeof(RefNode)) : s->bvh_node_count);
@@ -508,18 +604,8 @@ extern "C" int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *s)
     const size_t texels = (size_t)s->env_width * s->env_height;
     const size_t node_bytes = packer.out.size() * sizeof(PackedRecord);
     const size_t raw_tri = (size_t)s->triangle_count * 48, raw_env = texels * 12;
-    // the previous upload's staging must have drained before it is overwritten
-    if (!ctx->device_packed) RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    if (!ctx->device_packed && ctx->cap_stage < node_bytes) {
-        if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
-        ctx->h_stage = nullptr;
-        ctx->cap_stage = 0;
-        RT_CUDA(ctx, cudaMallocHost(&ctx->h_stage, std::max<size_t>(node_bytes, 64)));
-        ctx->cap_stage = std::max<size_t>(node_bytes, 64);
-    }
-    if (!ctx->device_packed) {
-        std::memcpy(ctx->h_stage, packer.out.data(), node_bytes);
-        if ((rc = upload(ctx, &ctx->d_nodes, &ctx->cap_nodes, ctx->h_stage, node_bytes)) != RT_OK) return rc;
+    if (!ctx->device_packed) {  // packer.out is pageable: the runtime stages the copy before cudaMemcpyAsync returns
+        if ((rc = upload(ctx, &ctx->d_nodes, &ctx->cap_nodes, packer.out.data(), node_bytes)) != RT_OK) return rc;
     }
     if ((rc = upload(ctx, &ctx->d_materials, &ctx->cap_materials, s->materials, (size_t)s->material_count * 48)) != RT_OK) return rc;
     if ((rc = upload(ctx, &ctx->d_spheres, &ctx->cap_spheres, s->spheres, (size_t)s->sphere_count * 16)) != RT_OK) return rc;
@@ -668,8 +754,9 @@ int enqueue_sort(rt_ctx *ctx, const uint32_t *count_ptr, size_t bound, int bits,
                  uint32_t **sorted_vals, int *launches)
 {
     int passes = std::min(kSortMaxPasses, std::max(1, (bits + 7) / 8));
-    size_t tiles = (ctx->sort_capacity + kSortTile - 1) / kSortTile;
-    uint32_t launch_tiles = (uint32_t)((bound + kSortTile - 1) / kSortTile);
+    size_t tiles = (ctx->sort_capacity + kSortTile - 1) / kSortTile;  // scratch is sized for the smallest tile
+    const int items = ctx->sort_items, tile_keys = kSortBlock * items;
+    uint32_t launch_tiles = (uint32_t)((bound + tile_keys - 1) / tile_keys);
     SortArgs s;
     s.count_ptr = count_ptr;
     s.hist = ctx->d_sort_scratch;
@@ -686,8 +773,20 @@ int enqueue_sort(rt_ctx *ctx, const uint32_t *count_ptr, size_t bound, int bits,
     sort_scan_kernel<<<passes, 256, 0, ctx->stream>>>(s);
     int src = 0;
     for (int p = 0; p < passes; p++) {
-        sort_scatter_kernel<<<launch_tiles, kSortBlock, 0, ctx->stream>>>(ctx->d_keys[src], (p == 0 && iota) ? nullptr : ctx->d_vals[src],
-                                                                          ctx->d_keys[src ^ 1], ctx->d_vals[src ^ 1], s, p);
+        const uint32_t *vin = (p == 0 && iota) ? nullptr : ctx->d_vals[src];
+#define RT_SCATTER(RANK, ITEMS) sort_scatter_kernel<RANK, ITEMS><<<launch_tiles, kSortBlock, 0, ctx->stream>>>(ctx->d_keys[src], vin, ctx->d_keys[src ^ 1], ctx->d_vals[src ^ 1], s, p)
+        switch (ctx->sort_rank * 100 + items) {
+        case 12: RT_SCATTER(0, 12); break;
+        case 16: RT_SCATTER(0, 16); break;
+        case 18: RT_SCATTER(0, 18); break;
+        case 112: RT_SCATTER(1, 12); break;
+        case 116: RT_SCATTER(1, 16); break;
+        case 118: RT_SCATTER(1, 18); break;
+        case 212: RT_SCATTER(2, 12); break;
+        case 216: RT_SCATTER(2, 16); break;
+        default: RT_SCATTER(2, 18); break;
+        }
+#undef RT_SCATTER
         src ^= 1;
     }
     RT_CUDA(ctx, cudaGetLastError());
@@ -808,7 +907,10 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         max_group = (int)std::max<size_t>(1, (free_b + have) / 10 * 7 / std::max<size_t>(1, per_pass));
     }
     max_group = std::max(1, std::min({max_group, (int)kMaxPassGroup, std::max(1, n_segs)}));
-    while (max_group > 1 && pass_rays_max * (size_t)max_group >= (1ull << 31)) max_group--;
+    // ray ids are 31-bit; the reorder pass keeps tile counts in 30 bits next to its two status flags (radix_sort.cuh)
+    const size_t wave_limit = sort ? (1ull << 30) : (1ull << 31);
+    if (pass_rays_max >= wave_limit) return fail(ctx, RT_ERR_INVALID, "rt_render: with sort = 1 width*height*pass_spp must be < 2^30");
+    while (max_group > 1 && pass_rays_max * (size_t)max_group >= wave_limit) max_group--;
     // PIPES (2 by default, RT_PIPES=1..4): consecutive waves rotate over that many streams, each with its own share of the queues and its own
     // counters. A wave is a chain of dependent launches whose late bounces hold a few 10^4 rays and whose persistent
     // tracer drains warp by warp at the end of every launch; with a second, independent wave in flight those SMs pick up
@@ -851,6 +953,18 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         for (int i = 0; i < pipes - 1; i++) RT_CUDA(ctx, cudaStreamWaitEvent(ctx->side[i], ctx->ev_fork, 0));
     }
 
+    // an error return from inside the loop must not leave launches in flight on the side streams (they write the queues and
+    // counters the next call reuses): drain every pipe on the way out
+    struct PipeGuard {
+        rt_ctx *c;
+        bool armed;
+        ~PipeGuard()
+        {
+            if (!armed) return;
+            for (cudaStream_t side : c->side) if (side) cudaStreamSynchronize(side);
+            cudaStreamSynchronize(c->stream);
+        }
+    } pipe_guard{ctx, true};
     int launches = 0, passes_done = 0, wave = 0;
     long long primaries = 0;
     // A WAVE is `group` consecutive passes of equal size traced together: every pass keeps the reference's seeds
@@ -937,6 +1051,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
     RT_CUDA(ctx, cudaGetLastError());
     RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    pipe_guard.armed = false;  // the main stream waited for every pipe (ev_join)
 
     if (stats) {
         std::memset(stats, 0, sizeof(*stats));
@@ -1125,7 +1240,7 @@ extern "C" int rt_process_rays(rt_ctx *ctx, float *ray_data12, const uint32_t *s
 
 extern "C" int rt_sort_pairs(rt_ctx *ctx, uint32_t *keys, uint32_t *values, int32_t n, int32_t bits)
 {
-    if (!ctx || !keys || !values || n < 0 || bits <= 0 || bits > 32) return fail(ctx, RT_ERR_INVALID, "rt_sort_pairs: bad argument");
+    if (!ctx || !keys || !values || n < 0 || n >= (1 << 30) || bits <= 0 || bits > 32) return fail(ctx, RT_ERR_INVALID, "rt_sort_pairs: bad argument (n must be < 2^30)");
     if (n == 0) return RT_OK;
     RT_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = RT_OK;
@@ -1168,6 +1283,41 @@ extern "C" int rt_sort_pairs(rt_ctx *ctx, uint32_t *keys, uint32_t *values, int3
 }
 extern "C" double rt_sort_device_ms(const rt_ctx *ctx) { return ctx ? ctx->sort_device_ms : 0.0; }
 
+// ---- bandwidth probe (bench.py's roofline denominators for the cache levels) ------------------------------------------
+namespace {
+__global__ void __launch_bounds__(256) probe_copy_kernel(const float4 *__restrict__ src, float4 *__restrict__ dst, size_t n, int reps)
+{
+    for (int r = 0; r < reps; r++)  // many sweeps inside ONE launch: a 32 MB sweep lasts a few microseconds, less than a launch gap
+        for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t)gridDim.x * 256) {
+            float4 v;
+            asm volatile("ld.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(src + i));  // volatile: every sweep loads
+            dst[i] = v;
+        }
+}
+}  // namespace
+
+extern "C" int rt_probe_copy_gbs(rt_ctx *ctx, int64_t bytes, int32_t iters, double *out_gbs)
+{
+    if (!ctx || !out_gbs || bytes < 4096 || iters <= 0) return fail(ctx, RT_ERR_INVALID, "rt_probe_copy_gbs: bad argument");
+    RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    DeviceBuffer a, b;
+    const size_t n = (size_t)bytes / 16;
+    RT_CUDA(ctx, cudaMalloc(&a.p, n * 16));
+    RT_CUDA(ctx, cudaMalloc(&b.p, n * 16));
+    RT_CUDA(ctx, cudaMemsetAsync(a.p, 1, n * 16, ctx->stream));
+    const int grid = (int)std::min<size_t>((size_t)ctx->sm_count * 8, (n + 255) / 256);
+    probe_copy_kernel<<<grid, 256, 0, ctx->stream>>>((const float4 *)a.p, (float4 *)b.p, n, 3);  // warm (and fill L2)
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev_start, ctx->stream));
+    probe_copy_kernel<<<grid, 256, 0, ctx->stream>>>((const float4 *)a.p, (float4 *)b.p, n, iters);
+    RT_CUDA(ctx, cudaEventRecord(ctx->ev_stop, ctx->stream));
+    RT_CUDA(ctx, cudaGetLastError());
+    RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    float ms = 0;
+    RT_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_start, ctx->ev_stop));
+    *out_gbs = 2.0 * (double)(n * 16) * iters / (ms * 1e-3) * 1e-9;
+    return RT_OK;
+}
+
 extern "C" uint32_t rt_index_divide(uint32_t n, uint32_t d) { return rtd::fast_div(n, rtd::make_fast_div(d)); }
 
 // ---- device BVH build: inspection hooks ---------------------------------------------------------------------------
@@ -1198,3 +1348,6 @@ extern "C" int rt_scene_download_bvh(rt_ctx *ctx, void *nodes32, int32_t node_ca
     }
     return RT_OK;
 }
+
+// ---- several GPUs of one box (rt_multi_*) ----------------------------------------------------------------------------
+#include "multi_device.cuh"

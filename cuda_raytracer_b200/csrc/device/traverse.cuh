@@ -115,19 +115,24 @@ __device__ __forceinline__ bool slab(float lox, float loy, float loz, float hix,
 #endif
 
 // scene.cu:338-372. Returns through closest/prim; runs before the BVH and seeds `closest`.
+// Contraction is forbidden (explicit _rn operations in the host's evaluation order, IEEE square root): the discriminant
+// b^2 - (|c - o|^2 - r^2) cancels catastrophically for the far, huge spheres of spheres.scene (radius 4e4 at 4e5: both terms
+// ~1.6e9 with an ulp of 128) and for every ray that STARTS on such a sphere, so a fused multiply-add moves a grazing root by
+// whole units. Written this way the sphere distance is bit-identical to the reference's host code (the oracle's sphere leg,
+// tests/test_gpu_parity.py::test_closest_hit_with_spheres); the loop runs over 0-4 spheres and costs nothing measurable.
 __device__ __forceinline__ void intersect_spheres(const DeviceScene &sc, float3 o, float3 d, float &closest, int &prim)
 {
     for (int i = 0; i < sc.sphere_count; i++) {
-        float4 s = __ldg(sc.spheres + i);
-        float3 offset = f3(s.x, s.y, s.z) - o;
-        float minus_half_b = dot(offset, d);
-        float quarter_c = length2(offset) - s.w * s.w;
-        float quarter_disc = minus_half_b * minus_half_b - quarter_c;
+        const float4 s = __ldg(sc.spheres + i);
+        const float3 offset = f3(__fsub_rn(s.x, o.x), __fsub_rn(s.y, o.y), __fsub_rn(s.z, o.z));
+        const float minus_half_b = dot_nofma(offset, d);
+        const float quarter_c = __fsub_rn(dot_nofma(offset, offset), __fmul_rn(s.w, s.w));
+        const float quarter_disc = __fsub_rn(__fmul_rn(minus_half_b, minus_half_b), quarter_c);
         if (quarter_disc < 0.0f) continue;
-        float half_root = sqrtf(quarter_disc);
-        float t = minus_half_b - half_root;
+        const float half_root = __fsqrt_rn(quarter_disc);
+        float t = __fsub_rn(minus_half_b, half_root);
         if (t < closest && t > kTMin) { closest = t; prim = i; continue; }
-        t = minus_half_b + half_root;
+        t = __fadd_rn(minus_half_b, half_root);
         if (t < closest && t > kTMin) { closest = t; prim = i; continue; }
     }
 }

@@ -2,7 +2,10 @@
 // (/root/reference/raytracing.cu:305-398): same argument grammar, exit codes (1 usage / CUDA error, 2 no hardware),
 // stdout lines and ./raytracing.png output. The render itself goes through the C ABI (rt_core.h); there is no CPU
 // renderer in this product, so `cpu` without a GPU path is refused with exit code 2 like "no hardware".
-// Extra words the reference would ignore: out=<path>, stats, no_bloom, device=<n>, gpu_bvh (build the BVH on the device), sbvh (host tree with spatial splits).
+// Extra words the reference would ignore: out=<path>, stats, no_bloom, device=<n>, gpus=<n> (split the frame's rays over the first
+// n GPUs, one NCCL reduce), host_bvh (build the BVH on the host as the reference does; the default is the same binned-SAH
+// build on the device, ~70x faster), gpu_bvh (the default, kept for old command lines), sbvh (host tree with spatial splits).
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -18,8 +21,8 @@ int main(int argc, char **argv)
         std::printf("Usage: %s <scene>\n", argv[0]);
         return 1;
     }
-    bool sort = true, cpu = false, gpu = true, bvh = true, bloom = true, stats_on = false, gpu_bvh = false, sbvh = false;
-    int device = 0;
+    bool sort = true, cpu = false, gpu = true, bvh = true, bloom = true, stats_on = false, gpu_bvh = true, sbvh = false;
+    int device = 0, gpus = 1;
     std::string out_path = "raytracing.png";
     for (int i = 2; i < argc; i++) {
         const char *w = argv[i];
@@ -30,7 +33,9 @@ int main(int argc, char **argv)
         else if (!std::strcmp(w, "no_bloom")) bloom = false;
         else if (!std::strcmp(w, "stats")) stats_on = true;
         else if (!std::strcmp(w, "gpu_bvh")) gpu_bvh = true;
-        else if (!std::strcmp(w, "sbvh")) sbvh = true;
+        else if (!std::strcmp(w, "host_bvh")) gpu_bvh = false;
+        else if (!std::strcmp(w, "sbvh")) { sbvh = true; gpu_bvh = false; }
+        else if (!std::strncmp(w, "gpus=", 5)) gpus = std::max(1, std::atoi(w + 5));
         else if (!std::strncmp(w, "out=", 4)) out_path = w + 4;
         else if (!std::strncmp(w, "device=", 7)) device = std::atoi(w + 7);
     }
@@ -50,8 +55,18 @@ int main(int argc, char **argv)
 
     auto t0 = std::chrono::high_resolution_clock::now();
     rt_ctx *ctx = nullptr;
-    int rc = rt_create(&ctx, device);
-    if (rc == RT_OK) rc = rt_scene_upload(ctx, &desc);
+    rt_multi *multi = nullptr;
+    int rc;
+    if (gpus > 1) {  // devices device, device + 1, ...
+        std::vector<int> devs;
+        for (int i = 0; i < gpus; i++) devs.push_back(device + i);
+        rc = rt_multi_create(&multi, devs.data(), gpus);
+        if (rc == RT_OK) ctx = rt_multi_context(multi, 0);
+        if (rc == RT_OK) rc = rt_multi_scene_upload(multi, &desc);
+    } else {
+        rc = rt_create(&ctx, device);
+        if (rc == RT_OK) rc = rt_scene_upload(ctx, &desc);
+    }
     if (rc == RT_OK && desc.triangles_form == 1) {  // the reference's two build lines (scene.cu:1023-1027), from the device build
         int32_t node_count = 0;
         rt_scene_download_bvh(ctx, nullptr, 0, &node_count, nullptr, 0);
@@ -61,28 +76,31 @@ int main(int argc, char **argv)
     opts.sort = sort ? 1 : 0;
     opts.collect_stats = stats_on ? 1 : 0;
     rt_stats st{};
-    if (rc == RT_OK) rc = rt_render_device(ctx, &opts, nullptr, &st);
+    if (rc == RT_OK) rc = multi ? rt_multi_render(multi, &opts, nullptr, &st) : rt_render_device(ctx, &opts, nullptr, &st);
     std::vector<uint8_t> rgb8((size_t)desc.width * desc.height * 3);
     if (rc == RT_OK) {
         double gpu_s = std::chrono::duration<double>(std::chrono::high_resolution_clock::now() - t0).count();
         std::printf("GPU Took %gs\n", gpu_s);  // same span as the reference's timer: allocation, upload, passes
-        rc = rt_postprocess(ctx, bloom ? 1 : 0, nullptr, rgb8.data());
+        rc = multi ? rt_multi_postprocess(multi, bloom ? 1 : 0, nullptr, rgb8.data()) : rt_postprocess(ctx, bloom ? 1 : 0, nullptr, rgb8.data());
     }
-    if (rc != RT_OK) {
-        std::printf("Error %s\n", rt_last_error(ctx));
-        rt_destroy(ctx);
+    auto teardown = [&]() {
+        if (multi) rt_multi_destroy(multi);
+        else rt_destroy(ctx);
         rt_scene_free(scene);
+    };
+    if (rc != RT_OK) {
+        std::printf("Error %s\n", multi ? rt_multi_last_error(multi) : rt_last_error(ctx));
+        teardown();
         return 1;
     }
     if (stats_on) {
         double mrays = st.live_ray_bounces / st.loop_seconds * 1e-6;
         std::printf("{\"loop_s\": %.6f, \"live_ray_bounces\": %lld, \"mrays_per_s\": %.1f, \"internal_visits\": %lld, "
-                    "\"triangle_tests\": %lld, \"launches\": %d, \"passes\": %d}\n",
+                    "\"triangle_tests\": %lld, \"launches\": %d, \"passes\": %d, \"gpus\": %d, \"reduce_ms\": %.3f}\n",
                     st.loop_seconds, (long long)st.live_ray_bounces, mrays, (long long)st.internal_visits,
-                    (long long)st.triangle_tests, st.kernel_launches, st.passes);
+                    (long long)st.triangle_tests, st.kernel_launches, st.passes, gpus, multi ? rt_multi_reduce_ms(multi) : 0.0);
     }
     rc = rt_write_png(out_path.c_str(), desc.width, desc.height, rgb8.data());
-    rt_destroy(ctx);
-    rt_scene_free(scene);
+    teardown();
     return rc == RT_OK ? 0 : 1;
 }

@@ -8,7 +8,22 @@
 
 struct rt_host_scene {
     rt::HostScene scene;
+    bool pinned = false;
 };
+
+namespace {
+// The big arrays a render context uploads (triangles, nodes, texels): page-locked for the scene's lifetime so that
+// rt_scene_upload's copies are asynchronous DMA. A no-op without a CUDA device (rt_host_pin reports it, nothing depends on it).
+template <class F>
+void for_each_big_array(rt_host_scene *h, F f)
+{
+    rt::HostScene &s = h->scene;
+    f(s.triangles.data(), s.triangles.size() * sizeof(rt::TriRecord));
+    f(s.nodes.data(), s.nodes.size() * sizeof(rt::TreeNode));
+    f(s.env.data(), s.env.size() * sizeof(float));
+    f(s.material_indices.data(), s.material_indices.size() * sizeof(uint16_t));
+}
+}  // namespace
 
 namespace rt {
 thread_local std::string g_last_error;  // shared with the device side (rt_last_error(NULL))
@@ -35,11 +50,19 @@ int rt_scene_load(const char *path, int use_bvh, int verbose, rt_host_scene **ou
         delete h;
         return RT_ERR_IO;
     }
+    if (rt_device_count() > 0) {
+        h->pinned = true;
+        for_each_big_array(h, [](const void *p, size_t bytes) { if (bytes >= 65536) rt_host_pin(p, bytes); });
+    }
     *out = h;
     return RT_OK;
 }
 
-void rt_scene_free(rt_host_scene *scene) { delete scene; }
+void rt_scene_free(rt_host_scene *scene)
+{
+    if (scene && scene->pinned) for_each_big_array(scene, [](const void *p, size_t bytes) { if (bytes >= 65536) rt_host_unpin(p); });
+    delete scene;
+}
 
 int rt_scene_describe(const rt_host_scene *h, rt_scene_desc *d)
 {

@@ -1,10 +1,12 @@
-"""Sample-split rendering across the GPUs of one box: one process per GPU, scene replicated, passes partitioned,
-accumulation buffers summed with one reduce to rank 0 (the reference itself is single-GPU).
+"""Sample-split rendering across the GPUs of one box: one process per GPU, scene replicated, the frame's ray sequence
+partitioned, accumulation buffers summed with one reduce to rank 0 (the reference itself is single-GPU).
 
-A pass (<= 20 samples per pixel, raytracing.cu:222-254) is the independent unit: its seeds depend only on the number of
-samples still to cast after it (raytracing.cu:229,236), so pass k produces the same rays on any GPU count and the
-N-GPU image equals the 1-GPU image up to float summation order. `torch.distributed` is plumbing only (NCCL on GPUs,
-gloo in the CPU tests); nothing here computes on the CPU.
+A pass (<= 20 samples per pixel, raytracing.cu:222-254) is an independent unit: its seeds depend only on the number of
+samples still to cast after it (raytracing.cu:229,236) and, per ray, on the ray's index inside the pass (raytracing.cu:89,
+scene.cu:81). So a pass can be cut at any ray: every rank takes an equal contiguous share of the frame's ray sequence
+(`ray_range`; whole passes when the pass count divides by the ranks, `pass_range`), ray k is the same ray on any GPU count
+and the N-GPU image equals the 1-GPU image up to float summation order. `torch.distributed` is plumbing only (NCCL on
+GPUs, gloo in the CPU tests); nothing here computes on the CPU.
 """
 import numpy as np
 
@@ -22,6 +24,20 @@ def pass_range(total_passes, rank, world):
     base, extra = divmod(total_passes, world)
     first = rank * base + min(rank, extra)
     return first, base + (1 if rank < extra else 0)
+
+
+def ray_range(total_rays, rank, world, align=1):
+    """Contiguous share [first, first + count) of the frame's ray sequence (pass 0's rays, then pass 1's, ...) for `rank`:
+    equal up to `align` rays (rt_render_opts.ray_first / ray_count). 50 passes on 8 GPUs = 6.25 passes each, where whole
+    passes would give 7 / 6 (89 % at best)."""
+    if world <= 0 or not (0 <= rank < world) or align <= 0:
+        raise ValueError("bad rank / world size")
+    units = (total_rays + align - 1) // align
+    base, extra = divmod(units, world)
+    first = rank * base + min(rank, extra)
+    count = base + (1 if rank < extra else 0)
+    lo, hi = min(total_rays, first * align), min(total_rays, (first + count) * align)
+    return lo, hi - lo
 
 
 class DeviceFramebuffer:
@@ -42,20 +58,24 @@ def render_distributed(renderer, scene, dist, rank, world, device_index, sort=Tr
     """Render this rank's share of the frame on its GPU and reduce to rank 0.
 
     Returns (sums float32[H, W, 3] on rank 0 else None, rt_stats of this rank). The scene must already be uploaded.
-    Ranks beyond the number of passes contribute zeros.
+    Ranks beyond the number of rays contribute zeros.
     """
     import torch
 
-    spp = pass_spp if pass_spp > 0 else PASS_SPP
-    total = pass_count(scene.desc().ray_count, spp)
-    first, count = pass_range(total, rank, world)
+    d = scene.desc()
+    total_rays = d.width * d.height * d.ray_count
+    first, count = ray_range(total_rays, rank, world)
     n = renderer.width * renderer.height * 3
-    ptr = renderer.render_device(sort=sort, pass_spp=pass_spp, pass_first=first if count else 0, pass_count=max(count, 1), **render_kw)
+    if world == 1:
+        ptr = renderer.render_device(sort=sort, pass_spp=pass_spp, **render_kw)
+    else:  # an empty share renders nothing (a range past the end) and leaves a zeroed framebuffer
+        ptr = renderer.render_device(sort=sort, pass_spp=pass_spp, ray_first=first if count else total_rays, ray_count=max(count, 1), **render_kw)
     stats = renderer.last_stats
     fb = torch.as_tensor(DeviceFramebuffer(ptr, n), device=f"cuda:{device_index}")
-    if count == 0:
-        fb.zero_()
     reduce_to_root(fb, dist if world > 1 else None, 0)
+    # The reduce runs on torch's stream and reads the core's framebuffer in place; the core's next render clears and
+    # accumulates into that buffer on ITS OWN stream. Wait for the reduce on every rank before handing control back.
+    torch.cuda.current_stream().synchronize()
     if rank != 0:
         return None, stats
     if out is None:

@@ -20,6 +20,7 @@
 #ifndef RT_CORE_H
 #define RT_CORE_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -130,6 +131,13 @@ void rt_destroy(rt_ctx *ctx);
 /* ctx may be NULL for errors of rt_create / the host scene layer (thread-local). */
 const char *rt_last_error(const rt_ctx *ctx);
 
+/* Optional: page-lock a caller-owned host array (scene arrays handed to rt_scene_upload, the output of rt_render) so that the
+ * copies are asynchronous DMA at PCIe speed instead of staged pageable copies (scene.cu:243-265 copies pageable memory). The
+ * caller must rt_host_unpin before freeing the array. rt_scene_load pins the arrays of the scenes it returns; without a CUDA
+ * device rt_host_pin returns RT_ERR_NO_DEVICE and nothing else changes. */
+int rt_host_pin(const void *ptr, size_t bytes);
+void rt_host_unpin(const void *ptr);
+
 /* Replaces Scene::copy_from_cpu_async + the __constant__ symbol (scene.cu:243-265, raytracing.cu:19):
  * packs the BVH into 64-byte two-child records and the triangles into 3 x float4, uploads all. */
 int rt_scene_upload(rt_ctx *ctx, const rt_scene_desc *scene);
@@ -157,6 +165,32 @@ int rt_postprocess(rt_ctx *ctx, int bloom, float *out_rgb_sum, uint8_t *out_rgb8
 /* Load sums into the device framebuffer (e.g. after a host-side combine); n = 3*W*H floats. */
 int rt_framebuffer_upload(rt_ctx *ctx, const float *rgb_sum);
 
+/* ---- several GPUs of one box --------------------------------------------------------------------------------------
+ * The reference's gpu_raytrace (raytracing.cu:170-284) drives one GPU. rt_multi_* is the same call over a list of
+ * devices: the scene is replicated, the frame's ray sequence is cut into equal contiguous shares (ray_first / ray_count
+ * above; every ray keeps the seeds of its pass and index, so the image equals the one-GPU image up to float summation
+ * order), each device renders its share from its own host thread, and ONE ncclReduce over NVLink sums the float
+ * accumulation buffers into devices[0]'s, where bloom and tone map run. The library owns the NCCL communicators
+ * (ncclCommInitAll at rt_multi_create; libnccl.so.2 is loaded at run time, the one-GPU entry points do not need it).
+ * A device list that names ONE device several times renders the shares on that device and sums them with a kernel
+ * (no NCCL): the same host path on a box with fewer GPUs. One host thread drives an rt_multi at a time. */
+typedef struct rt_multi rt_multi;
+int rt_multi_create(rt_multi **out, const int *devices, int n);
+void rt_multi_destroy(rt_multi *m);
+int rt_multi_device_count(const rt_multi *m);
+const char *rt_multi_last_error(const rt_multi *m);
+/* The per-device context (index 0 holds the combined frame after rt_multi_render); owned by the rt_multi. */
+rt_ctx *rt_multi_context(rt_multi *m, int index);
+int rt_multi_set_node_mode(rt_multi *m, int mode);
+int rt_multi_scene_upload(rt_multi *m, const rt_scene_desc *scene);
+/* As rt_render: out_rgb_sum (3*W*H floats, may be NULL when rt_multi_postprocess follows) receives the combined sums. A pass
+ * range or ray range in opts selects the rays to split. stats: counters summed over the devices, loop_seconds = the slowest
+ * device's pass loop + the reduce (CUDA events). */
+int rt_multi_render(rt_multi *m, const rt_render_opts *opts, float *out_rgb_sum, rt_stats *stats);
+/* CUDA-event time of the last combine step (ncclReduce, or the add kernels), milliseconds. */
+double rt_multi_reduce_ms(const rt_multi *m);
+int rt_multi_postprocess(rt_multi *m, int bloom, float *out_rgb_sum, uint8_t *out_rgb8);
+
 /* ---- kernel-level entry points (parity hooks; each runs the production device code) ---- */
 
 /* Closest hit of n rays {ox,oy,oz,dx,dy,dz}: Scene::bvh_closest_hit_distance (scene.cu:134-241), preceded by the
@@ -174,6 +208,10 @@ int rt_process_rays(rt_ctx *ctx, float *ray_data12, const uint32_t *seeds, int32
 int rt_sort_pairs(rt_ctx *ctx, uint32_t *keys, uint32_t *values, int32_t n, int32_t bits);
 /* CUDA-event time of the sort kernels of the last rt_sort_pairs call (copies excluded), in milliseconds. */
 double rt_sort_device_ms(const rt_ctx *ctx);
+/* Measurement aid: device-to-device copy of `bytes` (read + write counted) repeated `iters` times after a warm-up, GB/s by
+ * CUDA events. With a buffer pair that fits the L2 it gives the L2 bandwidth bench.py's roofline.l2_frac is quoted against;
+ * with a large one, the HBM copy bandwidth (the figure MEASURED_PEAKS.json holds). */
+int rt_probe_copy_gbs(rt_ctx *ctx, int64_t bytes, int32_t iters, double *out_gbs);
 /* Host mirror of the kernels' index arithmetic (ray id -> pass / pixel / row: n / d by multiply-and-shift with the constants
  * the render call derives from d). Needs no device; d = 0 is treated as 1. Test hook. */
 uint32_t rt_index_divide(uint32_t n, uint32_t d);

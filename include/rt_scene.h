@@ -1,4 +1,5 @@
-/* include/rt_scene.h — C ABI of the host scene layer (part of librtcore.so, pure host code, no CUDA calls).
+/* include/rt_scene.h — C ABI of the host scene layer (part of librtcore.so; host code: it works without a CUDA device, and with
+ * one its only CUDA call is rt_host_pin on the arrays of a loaded scene, so that uploads are asynchronous DMA).
  *
  * Replaces, on the host side of the render path:
  *     void load_scene(Scene *scene, const char *filename, bool use_bvh)   /root/reference/scene.cuh:168, scene.cu:569-831

@@ -3,7 +3,7 @@
  * CPU restatement of the reference's per-ray arithmetic, written from the behaviour described in
  * SURVEY.md §8a and the cited reference lines. Operation ORDER and the float/double mix follow
  * the reference expression by expression so the result is bit-identical to the reference's host
- * build with precise math (tests/test_oracle_vs_ref.py). Build: -ffp-contract=off, no fast-math.
+ * build with precise math (tests/test_oracle_golden.py against tests/golden/ref_vectors.npz). Build: -ffp-contract=off, no fast-math.
  */
 #include "rt_oracle.h"
 
@@ -389,40 +389,80 @@ void oracle_process(const oracle_scene *s, float *ray_data, const uint32_t *seed
 
 void oracle_render(const oracle_scene *s, int seed_mode, int pass_first, int pass_count, float *out_rgb, oracle_counters *counters)
 {
+    oracle_render_select(s, seed_mode, pass_first, pass_count, 0, -1, NULL, out_rgb, counters);
+}
+
+/* The pass loop restricted to a SUBSET of the frame's rays; every selected ray keeps the seeds of its own pass and of its
+ * index inside that pass (raytracing.cu:89,229,236, scene.cu:81), so the result is exactly that subset's contribution to
+ * the whole frame. Selection = passes [pass_first, pass_first + pass_count) (pass_count < 0: all), AND rays
+ * [ray_first, ray_first + ray_count) of the frame's ray sequence (pass 0's rays, then pass 1's, ...; ray_count < 0: all),
+ * AND pixels inside window = {x0, y0, w, h} (NULL: the whole image). out_rgb is the full-size image. */
+void oracle_render_select(const oracle_scene *s, int seed_mode, int pass_first, int pass_count, int64_t ray_first, int64_t ray_count,
+                          const int32_t *window, float *out_rgb, oracle_counters *counters)
+{
     int pixel_count = s->width * s->height;
-    float *ray_data = (float *)malloc(sizeof(float) * 12 * (size_t)pixel_count * ORACLE_PER_PASS);
     memset(out_rgb, 0, sizeof(float) * 3 * (size_t)pixel_count);
     int64_t live = 0, iv = 0, lv = 0, tt = 0;
     int remaining_rays = s->ray_count;
     int pass = 0;
+    int64_t sequence_start = 0;
+    int32_t *ids = NULL;
+    float *ray_data = NULL;
+    size_t cap = 0;
     while (remaining_rays) {
         int rays_to_cast = remaining_rays < ORACLE_PER_PASS ? remaining_rays : ORACLE_PER_PASS;
         remaining_rays -= rays_to_cast;
         int this_pass = pass++;
+        int64_t total_rays = (int64_t)rays_to_cast * pixel_count;
+        int64_t pass_start = sequence_start;
+        sequence_start += total_rays;
         if (this_pass < pass_first || (pass_count >= 0 && this_pass >= pass_first + pass_count)) continue;
-        int total_rays = rays_to_cast * pixel_count;
+        int64_t lo = 0, hi = total_rays;
+        if (ray_count >= 0) {
+            lo = ray_first - pass_start > 0 ? ray_first - pass_start : 0;
+            hi = ray_first + ray_count - pass_start < total_rays ? ray_first + ray_count - pass_start : total_rays;
+        }
+        if (hi <= lo) continue;
+        /* the selected ray indices of this pass */
+        size_t n_sel = 0;
+        if (window) {
+            size_t bound = (size_t)window[2] * window[3] * rays_to_cast;
+            if (bound > cap) { cap = bound; ids = (int32_t *)realloc(ids, sizeof(int32_t) * cap); ray_data = (float *)realloc(ray_data, sizeof(float) * 12 * cap); }
+            for (int y = window[1]; y < window[1] + window[3]; y++)
+                for (int x = window[0]; x < window[0] + window[2]; x++)
+                    for (int k = 0; k < rays_to_cast; k++) {
+                        int64_t i = ((int64_t)y * s->width + x) * rays_to_cast + k;
+                        if (i >= lo && i < hi) ids[n_sel++] = (int32_t)i;
+                    }
+        } else {
+            n_sel = (size_t)(hi - lo);
+            if (n_sel > cap) { cap = n_sel; ids = (int32_t *)realloc(ids, sizeof(int32_t) * cap); ray_data = (float *)realloc(ray_data, sizeof(float) * 12 * cap); }
+            for (size_t j = 0; j < n_sel; j++) ids[j] = (int32_t)(lo + (int64_t)j);
+        }
 #pragma omp parallel for schedule(dynamic, 1000)
-        for (int i = 0; i < total_rays; i++) generate_one(s, ray_data + 12 * (size_t)i, rays_to_cast, i, remaining_rays);
+        for (size_t j = 0; j < n_sel; j++) generate_one(s, ray_data + 12 * j, rays_to_cast, ids[j], remaining_rays);
         for (int b = 0; b < s->bounces; b++) {
 #pragma omp parallel for schedule(dynamic, 1000) reduction(+ : live, iv, lv, tt)
-            for (int i = 0; i < total_rays; i++) {
+            for (size_t j = 0; j < n_sel; j++) {
+                int i = ids[j];
                 pcg rng;
                 if (seed_mode == 0) /* raytracing.cu:148, shadowed loop variable => no bounce term (Q3) */
                     pcg_seed(&rng, (uint32_t)(1905678123 * i + 345903 * (remaining_rays * ORACLE_PER_PASS + i)));
                 else
                     pcg_seed(&rng, oracle_gpu_proc_seed(i, remaining_rays * ORACLE_PER_PASS + b));
                 oracle_counters c = {0, 0, 0, 0};
-                live += process_one(s, ray_data + 12 * (size_t)i, rng, counters ? &c : NULL);
+                live += process_one(s, ray_data + 12 * j, rng, counters ? &c : NULL);
                 iv += c.internal_visits; lv += c.leaf_visits; tt += c.triangle_tests;
             }
         }
-        for (int i = 0; i < total_rays; i++) { /* raytracing.cu:114-120, serial order */
-            float *px = out_rgb + 3 * (size_t)(i / rays_to_cast);
-            const float *col = ray_data + 12 * (size_t)i + 9;
+        for (size_t j = 0; j < n_sel; j++) { /* raytracing.cu:114-120, serial order */
+            float *px = out_rgb + 3 * (size_t)(ids[j] / rays_to_cast);
+            const float *col = ray_data + 12 * j + 9;
             px[0] += col[0]; px[1] += col[1]; px[2] += col[2];
         }
     }
     free(ray_data);
+    free(ids);
     if (counters) {
         counters->live_ray_bounces += live; counters->internal_visits += iv;
         counters->leaf_visits += lv; counters->triangle_tests += tt;

@@ -50,11 +50,32 @@ def test_command_line_writes_the_reference_outputs(tmp_path):
     assert "Node count: 1\n" in out2
     diff = np.sqrt(np.mean((img.astype(np.float64) - img2.astype(np.float64)) ** 2))
     assert diff < 6.0  # same streams, same geometry: only bloom-threshold flips and float order differ
-    img4, out4 = _run(EXE, tmp_path, scene, "gpu_bvh")  # tree built on the device: same node count, same picture
-    assert "Node count: 81311" in out4 and "BVH Took" in out4
+    img4, out4 = _run(EXE, tmp_path, scene, "host_bvh")  # tree built on the host as the reference does (the default builds it
+    assert "Node count: 81311" in out4 and "BVH Took" in out4  # on the device): same node count, same picture
     assert np.sqrt(np.mean((img.astype(np.float64) - img4.astype(np.float64)) ** 2)) < 6.0
     img3, out3 = _run(EXE, tmp_path, scene, "stats", "out=custom.png", png="custom.png")
     assert img3.shape == img.shape and '"mrays_per_s"' in out3 and not os.path.exists(tmp_path / "raytracing.png")
+
+
+def _gpu_count():
+    import cuda_raytracer_b200 as rt
+    return rt.device_count()
+
+
+@pytest.mark.parametrize("gpus", [2, 4, 8])
+def test_gpus_word_writes_the_same_png(tmp_path, gpus):
+    """`raytracing <scene> gpus=N` (rt_multi_*: ray-sequence split + one ncclReduce into device 0) writes the picture of
+    `gpus=1`: the rays are the same rays, only the float summation order differs (8-bit RMSE <= 0.5)."""
+    if _gpu_count() < gpus:
+        pytest.skip(f"needs {gpus} GPUs")
+    scene = _scene_copy(tmp_path, "lamp", 320, 180, 70, 6)  # 4 passes (20, 20, 20, 10): no GPU count divides the work evenly
+    one, out1 = _run(EXE, tmp_path, scene, "no_sort", "stats")
+    many, outn = _run(EXE, tmp_path, scene, "no_sort", "stats", f"gpus={gpus}")
+    assert f'"gpus": {gpus}' in outn
+    live = [int(re.search(r'"live_ray_bounces": (\d+)', o).group(1)) for o in (out1, outn)]
+    assert live[0] == live[1]
+    rmse = np.sqrt(np.mean((one.astype(np.float64) - many.astype(np.float64)) ** 2))
+    assert rmse <= 0.5, rmse
 
 
 @pytest.mark.parametrize("name,w,h,spp", [("cornell", 160, 160, 200), ("cornell_plus", 160, 160, 200), ("spheres", 200, 150, 200),

@@ -51,6 +51,23 @@ def test_lamp_4k_additivity_and_wave_invariance(renderer):
     assert np.allclose(sorted_img, parts[1], rtol=2e-4, atol=2e-4 * whole.mean())
 
 
+def test_crop_of_the_4k_frame_against_the_oracle(renderer):
+    """A 256 x 256 window of the headline configuration's frame (lamp 3840x2160, one pass of 20 spp, 10 bounces) against the
+    oracle's render of exactly those rays (oracle_render_select: same camera, same full-frame ray indices and seeds; ~4 M
+    ray-bounces on the CPU). Same bar as the small-image test: relative RMSE of the sums <= 2 %, mean within 0.2 %."""
+    from util import load, oracle_arrays, oracle_render_select
+    scene = load("lamp").set_image(W, H, 20, 10, 1.0)
+    renderer.upload(scene)
+    full = renderer.render(sort=False)
+    x0, y0, n = 1800, 900, 256  # on the lamp
+    want, ctr = oracle_render_select(oracle_arrays(scene), 1, window=(x0, y0, n, n))
+    got, ref = full[y0:y0 + n, x0:x0 + n], want[y0:y0 + n, x0:x0 + n]
+    assert ref.mean() > 0 and ctr.live_ray_bounces > 2 * n * n * 20
+    rel = np.sqrt(np.mean((got - ref) ** 2)) / np.sqrt(np.mean(ref ** 2))
+    assert rel <= 0.02, f"relative RMSE {rel:.4f}"
+    assert abs(got.mean() - ref.mean()) <= 2e-3 * ref.mean()
+
+
 def test_first_bounce_of_a_4k_pass_on_both_trees(renderer):
     """8.3 M primary rays (one per pixel) through trace_closest on the host-built and the device-built BVH."""
     host = rt.load_scene("lamp.scene", cwd=SCENES).set_image(W, H, 1, 1, 1.0)

@@ -26,6 +26,24 @@ def test_pass_range_partitions_every_pass_once():
         mg.pass_range(4, 2, 2)
 
 
+def test_ray_range_partitions_every_ray_once():
+    for total in (0, 1, 19, 1000 * 1000 * 1000, 3840 * 2160 * 640, 12345):
+        for world in (1, 2, 3, 8, 64):
+            for align in (1, 20, 640):
+                spans = [mg.ray_range(total, r, world, align) for r in range(world)]
+                pos = 0
+                for f, c in spans:
+                    assert c >= 0 and (c == 0 or f == pos)
+                    pos += c
+                assert pos == total
+                counts = [c for _, c in spans]
+                assert max(counts) - min(counts) <= (1 if align == 1 else 2 * align - 1)  # the last unit may be partial
+    # BASELINE configs[3]: teapot as shipped = 50 passes of 20 M rays on 8 GPUs -> 6.25 passes per rank
+    assert [mg.ray_range(10 ** 9, r, 8)[1] for r in range(8)] == [125_000_000] * 8
+    with pytest.raises(ValueError):
+        mg.ray_range(10, 3, 3)
+
+
 def _worker(rank, world, port, out_path):
     here = os.path.dirname(os.path.abspath(__file__))
     root = os.path.dirname(here)
@@ -35,7 +53,7 @@ def _worker(rank, world, port, out_path):
     import torch
     import torch.distributed as dist
 
-    from util import load, oracle_arrays, oracle_render
+    from util import load, oracle_arrays, oracle_render, oracle_render_select
 
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     try:
@@ -46,9 +64,17 @@ def _worker(rank, world, port, out_path):
         part = oracle_render(A, 1, first, count)[0] if count else np.zeros((A.height, A.width, 3), np.float32)
         t = torch.from_numpy(part.reshape(-1).copy())
         mg.reduce_to_root(t, dist, 0)
+        # the equal-share split of the ray sequence (4 passes on 3 ranks cut passes in the middle)
+        rf, rc = mg.ray_range(A.width * A.height * A.ray_count, rank, world)
+        part2, ctr = oracle_render_select(A, 1, ray_first=rf, ray_count=rc)
+        t2 = torch.from_numpy(part2.reshape(-1).copy())
+        live = torch.tensor([ctr.live_ray_bounces], dtype=torch.int64)
+        mg.reduce_to_root(t2, dist, 0)
+        dist.reduce(live, dst=0, op=dist.ReduceOp.SUM)
         if rank == 0:
-            whole = oracle_render(A, 1)[0]
-            np.savez(out_path, combined=t.numpy().reshape(whole.shape), whole=whole)
+            whole, cw = oracle_render(A, 1)
+            np.savez(out_path, combined=t.numpy().reshape(whole.shape), combined_rays=t2.numpy().reshape(whole.shape), whole=whole,
+                     live=np.array([int(live[0]), cw.live_ray_bounces]))
     finally:
         dist.destroy_process_group()
 
@@ -65,4 +91,6 @@ def test_two_rank_split_equals_whole_frame(tmp_path, world):
     mp.spawn(_worker, args=(world, port, out), nprocs=world, join=True)
     z = np.load(out)
     assert np.allclose(z["combined"], z["whole"], rtol=1e-5, atol=1e-5 * float(z["whole"].mean()))
+    assert np.allclose(z["combined_rays"], z["whole"], rtol=1e-5, atol=1e-5 * float(z["whole"].mean()))
+    assert z["live"][0] == z["live"][1]
     assert z["whole"].mean() > 0

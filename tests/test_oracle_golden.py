@@ -163,6 +163,33 @@ def test_render_pass_split_adds_up():
     assert sum(p[1].live_ray_bounces for p in parts) == c.live_ray_bounces
 
 
+def test_render_select_subsets_add_up():
+    """oracle_render_select: ray ranges of the frame's sequence and pixel windows keep every ray's own seeds, so disjoint
+    subsets sum to the golden-pinned oracle_render frame, counters included (the checker of the product's ray-range split
+    and of the 4K crop test)."""
+    from util import oracle_render_select
+    scene = load("cornell_plus").set_image(32, 24, 50, 5, 1.0)  # 3 passes: 20, 20, 10
+    A = oracle_arrays(scene)
+    whole, cw = oracle_render(A, 1)
+    total = 32 * 24 * 50
+    cuts = [0, 7, 32 * 24 * 20 - 1, 32 * 24 * 20 + 13, 32 * 24 * 45, total]
+    acc, live = np.zeros_like(whole, dtype=np.float64), 0
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        img, c = oracle_render_select(A, 1, ray_first=a, ray_count=b - a)
+        acc += img
+        live += c.live_ray_bounces
+    assert live == cw.live_ray_bounces
+    assert np.allclose(acc, whole, rtol=1e-5, atol=1e-6)
+    win, c1 = oracle_render_select(A, 1, window=(5, 3, 16, 9))
+    assert win[3:12, 5:21].tobytes() == whole[3:12, 5:21].tobytes()  # same rays, same per-pixel summation order
+    outside = win.copy()
+    outside[3:12, 5:21] = 0
+    assert not outside.any() and 0 < c1.live_ray_bounces < cw.live_ray_bounces
+    one, _ = oracle_render_select(A, 1, pass_first=1, pass_count=1)
+    ref, _ = oracle_render(A, 1, 1, 1)
+    assert one.tobytes() == ref.tobytes()
+
+
 def test_sort_key_degenerate_as_in_reference():
     """The reference key (scene.cu:44-60,480-485) collapses to at most 64 live values + 0xFFFFFFFF (Q1)."""
     scene = load("teapot").set_image(32, 24, 20, 4, 1.0)

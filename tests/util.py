@@ -66,6 +66,18 @@ def oracle_render(arrays, seed_mode=1, pass_first=0, pass_count=-1):
     return img, c
 
 
+def oracle_render_select(arrays, seed_mode=1, pass_first=0, pass_count=-1, ray_first=0, ray_count=-1, window=None):
+    """The oracle's pass loop over a subset of the frame's rays (pass range, ray range of the frame's sequence, pixel window
+    (x0, y0, w, h)); full-size image out."""
+    S = arrays.oracle_struct()
+    img = np.zeros((arrays.height, arrays.width, 3), np.float32)
+    c = po.Counters()
+    win = np.array(window, np.int32) if window is not None else None
+    po.port().oracle_render_select(C.byref(S), seed_mode, pass_first, pass_count, int(ray_first), int(ray_count),
+                                   win.ctypes.data if win is not None else None, img.reshape(-1), C.byref(c))
+    return img, c
+
+
 def scene_diag(arrays):
     """Diagonal of the triangle root box (1.0 when there are no triangles)."""
     if not len(arrays.triangles):
