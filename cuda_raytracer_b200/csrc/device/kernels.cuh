@@ -19,7 +19,7 @@
 
 namespace rtd {
 
-constexpr int kBlock = 128;        // threads per CTA of the traversal kernels
+constexpr int kBlock = kTraceBlock;  // threads per CTA of the traversal kernels (128)
 constexpr int kBlocksPerSM = 6;       // process_kernel (parity hook): full-depth stack in shared memory, 6 x 32 KB
 #ifndef RT_TRACE_CTAS
 #define RT_TRACE_CTAS 9

@@ -3,7 +3,7 @@
 //
 // Structure ("one sweep per digit"):
 //   1. sort_histogram_kernel: ONE read of the keys builds the global histograms of every digit position.
-//   2. sort_scan_kernel: exclusive scan of each 256-bin histogram (tiny).
+//   2. its last CTA scans each 256-bin histogram into exclusive offsets (no separate launch).
 //   3. sort_scatter_kernel, once per digit: each CTA takes the next tile (dynamic tile id), ranks its keys stably
 //      (warp match + per-warp counters in shared memory), obtains its global offset per digit by decoupled look-back
 //      over the tile-status array, and scatters keys and values. 8 B read + 8 B written per pair per digit.
@@ -18,7 +18,7 @@
 namespace rtd {
 
 constexpr int kSortBlock = 256;
-constexpr int kSortItems = 18;                          // keys per thread (RT_SORT_ITEMS selects among the instantiated 12 / 16 / 18; 48 KB of static shared memory caps it)
+constexpr int kSortItems = 22;                          // keys per thread (RT_SORT_ITEMS selects among the instantiated 12 / 16 / 18 / 22 / 26)
 constexpr int kSortTile = kSortBlock * 12;              // SMALLEST tile among the variants: sizes the tile-status scratch
 constexpr int kSortWarps = kSortBlock / 32;
 constexpr int kSortMaxPasses = 4;
@@ -36,9 +36,13 @@ struct SortArgs {
     uint32_t max_tiles;
 };
 
+// One read of the keys -> global histograms of every digit position; the LAST CTA to finish turns them into exclusive
+// offsets (one launch less per sort than a separate scan kernel). s.tile_counter[kSortMaxPasses] counts the finished CTAs.
 __global__ void __launch_bounds__(kSortBlock) sort_histogram_kernel(const uint32_t *__restrict__ keys, SortArgs s)
 {
     __shared__ uint32_t h[kSortMaxPasses][256];
+    __shared__ uint32_t warp_sum[8];
+    __shared__ bool last;
     for (int p = 0; p < s.passes; p++) h[p][threadIdx.x] = 0;
     __syncthreads();
     const uint32_t n = *s.count_ptr;
@@ -51,24 +55,28 @@ __global__ void __launch_bounds__(kSortBlock) sort_histogram_kernel(const uint32
         uint32_t v = h[p][threadIdx.x];
         if (v) atomicAdd(&s.hist[p * 256 + threadIdx.x], v);
     }
-}
-
-// one CTA of 256 threads per digit position: exclusive scan in place
-__global__ void __launch_bounds__(256) sort_scan_kernel(SortArgs s)
-{
-    __shared__ uint32_t warp_sum[8];
-    uint32_t *h = s.hist + blockIdx.x * 256;
-    uint32_t v = h[threadIdx.x], incl = v;
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    for (int off = 1; off < 32; off <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
-        if (lane >= (uint32_t)off) incl += t;
-    }
-    if (lane == 31) warp_sum[warp] = incl;
+    __threadfence();
     __syncthreads();
-    uint32_t base = 0;
-    for (uint32_t w = 0; w < warp; w++) base += warp_sum[w];
-    h[threadIdx.x] = base + incl - v;
+    if (threadIdx.x == 0) last = atomicAdd(&s.tile_counter[kSortMaxPasses], 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    for (int p = 0; p < s.passes; p++) {  // exclusive scan of each 256-bin histogram, in place
+        volatile uint32_t *hp = s.hist + p * 256;
+        const uint32_t v = hp[threadIdx.x];
+        uint32_t incl = v;
+        for (int off = 1; off < 32; off <<= 1) {
+            uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+            if (lane >= (uint32_t)off) incl += t;
+        }
+        if (lane == 31) warp_sum[warp] = incl;
+        __syncthreads();
+        uint32_t base = 0;
+        for (uint32_t w = 0; w < warp; w++) base += warp_sum[w];
+        hp[threadIdx.x] = base + incl - v;
+        __syncthreads();
+    }
 }
 
 // One digit pass. values_in == nullptr means "value = element index" (first pass of a fresh permutation).
@@ -93,7 +101,8 @@ __global__ void __launch_bounds__(kSortBlock, 3) sort_scatter_kernel(const uint3
     __shared__ uint32_t digit_base[256];             // global position of the tile's first key of each digit MINUS its position in the tile
     __shared__ uint32_t digit_start[256];            // position of that key inside the digit-ordered tile
     __shared__ uint32_t warp_total[kSortWarps];
-    __shared__ uint32_t stage_key[TILE], stage_val[TILE];
+    extern __shared__ uint32_t sort_stage[];         // dynamic (tiles above 18 keys per thread pass the 48 KB static limit): keys, then values
+    uint32_t *stage_key = sort_stage, *stage_val = sort_stage + TILE;
     __shared__ uint32_t tile_id_sh;
 
     const uint32_t n = *s.count_ptr;

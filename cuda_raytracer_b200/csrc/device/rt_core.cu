@@ -334,7 +334,7 @@ static int init_context(rt_ctx *ctx, int device)
     if (const char *e = std::getenv("RT_SHADE_PER_SM")) ctx->shade_per_sm = std::max(0, std::atoi(e));
     if (const char *e = std::getenv("RT_NODES")) ctx->node_mode = std::strcmp(e, "q16") == 0 ? kNodesQ16 : std::strcmp(e, "w4") == 0 ? kNodesW4 : kNodesF32;
     if (const char *e = std::getenv("RT_SORT_RANK")) ctx->sort_rank = std::min(2, std::max(0, std::atoi(e)));
-    if (const char *e = std::getenv("RT_SORT_ITEMS")) { const int v = std::atoi(e); ctx->sort_items = v <= 12 ? 12 : (v >= 18 ? 18 : 16); }
+    if (const char *e = std::getenv("RT_SORT_ITEMS")) { const int v = std::atoi(e); ctx->sort_items = v <= 12 ? 12 : v <= 16 ? 16 : v <= 18 ? 18 : v <= 22 ? 22 : 26; }
     if (const char *e = std::getenv("RT_ENTRY_K")) ctx->entry_max = std::min((int)kEntryMax, std::max(0, std::atoi(e)));
     if (const char *e = std::getenv("RT_BATCH")) ctx->trace_batch = (uint32_t)std::min(4096, std::max(4, std::atoi(e)));
     if (const char *e = std::getenv("RT_NODEMIN")) ctx->trace_node_min = (uint32_t)std::min(33, std::max(0, std::atoi(e)));
@@ -754,8 +754,8 @@ int enqueue_sort(rt_ctx *ctx, const uint32_t *count_ptr, size_t bound, int bits,
                  uint32_t **sorted_vals, int *launches)
 {
     int passes = std::min(kSortMaxPasses, std::max(1, (bits + 7) / 8));
-    size_t tiles = (ctx->sort_capacity + kSortTile - 1) / kSortTile;  // scratch is sized for the smallest tile
     const int items = ctx->sort_items, tile_keys = kSortBlock * items;
+    const size_t tiles = (ctx->sort_capacity + tile_keys - 1) / tile_keys;  // stride of the per-pass status arrays (the scratch is sized for the smallest tile)
     uint32_t launch_tiles = (uint32_t)((bound + tile_keys - 1) / tile_keys);
     SortArgs s;
     s.count_ptr = count_ptr;
@@ -764,17 +764,27 @@ int enqueue_sort(rt_ctx *ctx, const uint32_t *count_ptr, size_t bound, int bits,
     s.tile_status = ctx->d_sort_scratch + kSortMaxPasses * 256 + 16;
     s.passes = passes;
     s.max_tiles = (uint32_t)tiles;
-    // zero histograms, tile counters and the status words of the tiles this launch can touch
-    RT_CUDA(ctx, cudaMemsetAsync(ctx->d_sort_scratch, 0, (kSortMaxPasses * 256 + 16) * sizeof(uint32_t), ctx->stream));
-    for (int p = 0; p < passes; p++)
-        RT_CUDA(ctx, cudaMemsetAsync(s.tile_status + (size_t)p * tiles * 256, 0, (size_t)launch_tiles * 256 * sizeof(uint32_t), ctx->stream));
+    // zero histograms, tile counters and the status words of the tiles this launch can touch: ONE memset when the status
+    // arrays of the passes are adjacent (the launch covers the whole capacity, or one pass), else one per pass
+    const size_t head_words = kSortMaxPasses * 256 + 16;
+    if (launch_tiles == tiles || passes == 1) {
+        RT_CUDA(ctx, cudaMemsetAsync(ctx->d_sort_scratch, 0, (head_words + ((size_t)(passes - 1) * tiles + launch_tiles) * 256) * sizeof(uint32_t), ctx->stream));
+    } else {
+        RT_CUDA(ctx, cudaMemsetAsync(ctx->d_sort_scratch, 0, head_words * sizeof(uint32_t), ctx->stream));
+        for (int p = 0; p < passes; p++)
+            RT_CUDA(ctx, cudaMemsetAsync(s.tile_status + (size_t)p * tiles * 256, 0, (size_t)launch_tiles * 256 * sizeof(uint32_t), ctx->stream));
+    }
     int hist_blocks = (int)std::min<size_t>((size_t)ctx->sm_count * 8, std::max<size_t>(1, (bound + kSortBlock - 1) / kSortBlock));
-    sort_histogram_kernel<<<hist_blocks, kSortBlock, 0, ctx->stream>>>(ctx->d_keys[0], s);
-    sort_scan_kernel<<<passes, 256, 0, ctx->stream>>>(s);
+    sort_histogram_kernel<<<hist_blocks, kSortBlock, 0, ctx->stream>>>(ctx->d_keys[0], s);  // its last CTA scans the histograms
     int src = 0;
     for (int p = 0; p < passes; p++) {
         const uint32_t *vin = (p == 0 && iota) ? nullptr : ctx->d_vals[src];
-#define RT_SCATTER(RANK, ITEMS) sort_scatter_kernel<RANK, ITEMS><<<launch_tiles, kSortBlock, 0, ctx->stream>>>(ctx->d_keys[src], vin, ctx->d_keys[src ^ 1], ctx->d_vals[src ^ 1], s, p)
+#define RT_SCATTER(RANK, ITEMS)                                                                                                   \
+    do {                                                                                                                          \
+        constexpr int kStage = kSortBlock * ITEMS * 8;                                                                            \
+        if (kStage > 40 * 1024) cudaFuncSetAttribute(sort_scatter_kernel<RANK, ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStage); \
+        sort_scatter_kernel<RANK, ITEMS><<<launch_tiles, kSortBlock, kStage, ctx->stream>>>(ctx->d_keys[src], vin, ctx->d_keys[src ^ 1], ctx->d_vals[src ^ 1], s, p); \
+    } while (0)
         switch (ctx->sort_rank * 100 + items) {
         case 12: RT_SCATTER(0, 12); break;
         case 16: RT_SCATTER(0, 16); break;
@@ -784,6 +794,8 @@ int enqueue_sort(rt_ctx *ctx, const uint32_t *count_ptr, size_t bound, int bits,
         case 118: RT_SCATTER(1, 18); break;
         case 212: RT_SCATTER(2, 12); break;
         case 216: RT_SCATTER(2, 16); break;
+        case 222: RT_SCATTER(2, 22); break;
+        case 226: RT_SCATTER(2, 26); break;
         default: RT_SCATTER(2, 18); break;
         }
 #undef RT_SCATTER
@@ -792,7 +804,7 @@ int enqueue_sort(rt_ctx *ctx, const uint32_t *count_ptr, size_t bound, int bits,
     RT_CUDA(ctx, cudaGetLastError());
     *sorted_keys = ctx->d_keys[src];
     *sorted_vals = ctx->d_vals[src];
-    if (launches) *launches += 2 + passes;
+    if (launches) *launches += 1 + passes;
     return RT_OK;
 }
 

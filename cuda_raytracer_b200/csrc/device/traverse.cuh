@@ -195,14 +195,32 @@ __device__ __forceinline__ Uint8 ldg256u(const void *p)
 #ifndef RT_FAST_RCP
 #define RT_FAST_RCP 1
 #endif
+// RT_TRI_FTZ (default 1): rcp.approx.ftz is ONE MUFU.RCP; without .ftz ptxas wraps it in a range scaling (2 FSETP + 2 FSEL + 2
+// FMUL) for subnormal and huge operands. A subnormal determinant (|a| < 1.2e-38: a triangle ~1e-19 across) is then treated as
+// the reference treats a == 0 (no hit); NaN still falls through the compares as in the reference.
+#ifndef RT_TRI_FTZ
+#define RT_TRI_FTZ 1
+#endif
 __device__ __forceinline__ float tri_rcp(float a)
 {
-#if RT_FAST_RCP
+#if RT_FAST_RCP && RT_TRI_FTZ
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+    return r;
+#elif RT_FAST_RCP
     float r;
     asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(a));
     return r;
 #else
     return 1.0f / a;
+#endif
+}
+__device__ __forceinline__ bool tri_degenerate(float a)
+{
+#if RT_FAST_RCP && RT_TRI_FTZ
+    return fabsf(a) < 1.17549435e-38f;
+#else
+    return a == 0.0f;
 #endif
 }
 
@@ -216,7 +234,7 @@ __device__ __forceinline__ void intersect_triangle(const float4 *__restrict__ tr
     float3 p1 = f3(t8.lo.x, t8.lo.y, t8.lo.z), e1 = f3(t8.lo.w, t8.hi.x, t8.hi.y), e2 = f3(t8.hi.z, t8.hi.w, e2z);
     float3 h = cross(d, e2);
     float a = dot(h, e1);
-    if (a == 0.0f) return;
+    if (tri_degenerate(a)) return;
     float inv_a = tri_rcp(a);
     float3 s = o - p1;
     float u = dot(s, h) * inv_a;
@@ -228,6 +246,93 @@ __device__ __forceinline__ void intersect_triangle(const float4 *__restrict__ tr
     if (t <= kTMin || t >= closest) return;  // NaN passes, exactly as the reference's two compares do
     closest = t;
     prim = prim_base + (int)tri;
+}
+
+// The same test as a pure function: t of an accepted hit (kTMin < t < limit), else kNoTriHit.
+constexpr float kNoTriHit = 3e38f;
+__device__ __forceinline__ float triangle_t(const float4 *__restrict__ tris, uint32_t tri, float3 o, float3 d, float limit)
+{
+    const float4 *t4 = tris + 4 * (size_t)tri;
+    const Float8 t8 = ldg256(t4);
+    const float e2z = __ldg(reinterpret_cast<const float *>(t4 + 2));
+    float3 p1 = f3(t8.lo.x, t8.lo.y, t8.lo.z), e1 = f3(t8.lo.w, t8.hi.x, t8.hi.y), e2 = f3(t8.hi.z, t8.hi.w, e2z);
+    float3 h = cross(d, e2);
+    float a = dot(h, e1);
+    float inv_a = tri_rcp(a);
+    float3 s = o - p1;
+    float u = dot(s, h) * inv_a;
+    float3 q = cross(s, e1);
+    float v = dot(d, q) * inv_a;
+    float t = dot(e2, q) * inv_a;
+    const bool hit = !tri_degenerate(a) && u >= 0.0f && u <= 1.0f && v >= 0.0f && u + v <= 1.0f && t > kTMin && t < limit;
+    return hit ? t : kNoTriHit;
+}
+
+// RT_LEAF_SHARE (A/B, default 0 — measured 20 % SLOWER on lamp 4K, 15 % on teapot, 28 % on cornell_plus, profiles/r2b_tracer.md:
+// the sequential test leaves early at the first failed barycentric check, ~3.9 warp instructions per test and ray as profiled,
+// while the dealt-out test runs to the end and pays ~70 instructions of scan / shuffle / segmented-minimum overhead per round):
+// the leaf phase of a warp as ONE collective step. After the descent loop ~14 of the 32 lanes hold a
+// leaf of 1-4 triangles; tested lane by lane (loop over each lane's count) that is 3-4 rounds of a ~50-instruction test at
+// 7-14 active lanes, each round waiting for its own triangle loads: 30 % of the tracer's warp instructions at 12 lanes and its
+// largest block of stall samples on the incoherent bounces (profiles/r2a). Here the warp's (ray, triangle) pairs are numbered
+// with a prefix sum over the lanes' counts and dealt out to all 32 lanes, 32 pairs per round: a lane fetches the owner's ray
+// with shuffles, tests ONE triangle, and a segmented minimum over the pair's neighbours hands the nearest accepted hit back to
+// the owner. Ties go to the lower triangle index and every test sees the owner's distance limit from before the leaf, so the
+// result equals the sequential loop's (which accepts t < closest in index order). A NaN distance is dropped here where the
+// sequential form (and the reference) would accept it: only inputs with NaN / infinite coordinates produce one.
+#ifndef RT_LEAF_SHARE
+#define RT_LEAF_SHARE 0
+#endif
+template <bool STATS>
+__device__ __forceinline__ void leaf_phase_shared(const DeviceScene &sc, bool has_leaf, uint32_t cur, float3 o, float3 d, float &closest,
+                                                  int &prim, uint32_t *table, TraceCounters &ctr)
+{
+    constexpr uint32_t FULL = 0xffffffffu;
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t c = has_leaf ? ((cur >> kLeafCountShift) & 15u) : 0u;
+    const uint32_t first = cur & kLeafStartMask;
+    if (STATS) ctr.triangle_tests += c;
+    uint32_t incl = c;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t t = __shfl_up_sync(FULL, incl, off);
+        if (lane >= (uint32_t)off) incl += t;
+    }
+    const uint32_t total = __shfl_sync(FULL, incl, 31);
+    const uint32_t s = incl - c;  // this owner's first pair
+    float best_t = closest;
+    uint32_t best_k = 0xffffffffu;
+    for (uint32_t base = 0; base < total; base += 32u) {
+        const uint32_t lo = max(s, base), hi = min(s + c, base + 32u);
+        for (uint32_t x = lo; x < hi; x++) table[x - base] = lane | ((x - s) << 8);  // pair -> (owner lane, triangle of its leaf)
+        __syncwarp();
+        const bool valid = base + lane < total;
+        const uint32_t e = valid ? table[lane] : lane;
+        const uint32_t own = e & 31u;
+        uint32_t kk = e >> 8;
+        const float3 ro = f3(__shfl_sync(FULL, o.x, own), __shfl_sync(FULL, o.y, own), __shfl_sync(FULL, o.z, own));
+        const float3 rd = f3(__shfl_sync(FULL, d.x, own), __shfl_sync(FULL, d.y, own), __shfl_sync(FULL, d.z, own));
+        const float limit = __shfl_sync(FULL, closest, own);
+        const uint32_t tri = __shfl_sync(FULL, first, own) + kk;
+        float t = kNoTriHit;
+        if (valid) t = triangle_t(sc.tris, tri, ro, rd, limit);
+        // segmented minimum: the pairs of one owner sit in consecutive lanes (at most 15), lower lane = lower triangle index
+#pragma unroll
+        for (int off = 1; off < 16; off <<= 1) {
+            const float t2 = __shfl_down_sync(FULL, t, off);
+            const uint32_t k2 = __shfl_down_sync(FULL, kk, off), o2 = __shfl_down_sync(FULL, own, off);
+            if (lane + (uint32_t)off < 32u && o2 == own && t2 < t) { t = t2; kk = k2; }
+        }
+        const uint32_t head = hi > lo ? lo - base : 0u;  // the owner's first pair of this round holds its minimum
+        const float rt = __shfl_sync(FULL, t, head);
+        const uint32_t rk = __shfl_sync(FULL, kk, head);
+        if (hi > lo && rt < best_t) { best_t = rt; best_k = rk; }
+        __syncwarp();  // the table is rewritten by the next round
+    }
+    if (best_k != 0xffffffffu) {
+        closest = best_t;
+        prim = sc.sphere_count + (int)(first + best_k);
+    }
 }
 
 template <int BLOCK, bool STATS>
@@ -290,6 +395,7 @@ __device__ __forceinline__ void traverse_bvh(const DeviceScene &sc, float3 o, fl
 // IO policy:  bool load(uint32_t i, float3 &o, float3 &d, float &closest, int &prim)   false = nothing to trace
 //             void store(uint32_t i, float closest, int prim)
 //             void begin(uint32_t i, Stack &stack, int &sp, uint32_t &cur)           where the walk of ray i starts
+constexpr int kTraceBlock = 128;            // threads per CTA of the tracer kernels
 constexpr uint32_t kDoneRef = 0xFFFFFFFFu;  // never a valid leaf ref: start would exceed the 2^27 triangle limit
 constexpr int kBatch = 512;                 // default: rays a warp claims per global atomic (re-swept in r1m: 192 -> 512 = +0.6-1 %)
 constexpr int kRefillBelow = 16;           // default: refill when fewer lanes than this still hold a ray
@@ -303,6 +409,12 @@ struct TraceTuning {
     uint32_t node_min;      // leave the descent loop when fewer lanes than this are still descending
 };
 
+// RT_BRANCHFREE (A/B, default 0): child selection after the two box tests as one straight-line sequence instead of four branch
+// bodies. Measured -0.7 % (lamp 4K), -1.1 % (teapot), -0.7 % (cornell_plus): the bodies are short and ptxas already predicates
+// most of them; the straight-line form makes every lane pay for the push (profiles/r2b_tracer.md).
+#ifndef RT_BRANCHFREE
+#define RT_BRANCHFREE 0
+#endif
 #ifndef RT_STACK_TOP
 #define RT_STACK_TOP 8
 #endif
@@ -361,6 +473,9 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
 #else
     constexpr uint32_t refill_below = kRefillBelow, node_min = kNodeMin;
 #endif
+#if RT_LEAF_SHARE
+    __shared__ uint32_t leaf_table[kTraceBlock];  // 32 entries per warp: (owner lane, triangle) of the pairs of one leaf round
+#endif
     uint32_t pool_next = 0, pool_end = 0;  // warp-uniform: unclaimed part of the current batch
     bool exhausted = false;                // warp-uniform: the global cursor ran past n
     bool busy = false;
@@ -414,6 +529,121 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
             continue;
         }
 
+#if RT_LEAF_SHARE
+        // ---- walk in warp-uniform rounds: descent (lane by lane) -> collective leaf phase -> pop / retire ----
+        for (;;) {
+            if (busy) {
+            // descend through internal records until this lane holds a leaf (or runs dry)
+            while (!(cur & kLeafBit)) {
+                if (STATS) ctr.internal_visits++;
+                if (NODES == kNodesW4) {
+                    // 4-wide node: two 32-byte halves {children 0,1} {children 2,3}; hit children sorted by entry distance
+                    // (5 compare-exchanges), the nearest becomes the current reference, the others go on the stack far first
+                    const uint4 *nd = qnodes + 4 * (size_t)cur;
+                    const Uint8 na = ldg256u(nd), nb = ldg256u(nd + 2);
+                    constexpr float kNoHit = 3e38f;
+                    float e0, e1, e2, e3;
+                    const bool h0 = slab_q(na.lo.x, na.lo.y, na.lo.z, qr, closest, e0), h1 = slab_q(na.lo.w, na.hi.x, na.hi.y, qr, closest, e1);
+                    const bool h2 = slab_q(nb.lo.x, nb.lo.y, nb.lo.z, qr, closest, e2), h3 = slab_q(nb.lo.w, nb.hi.x, nb.hi.y, qr, closest, e3);
+                    float k0 = h0 ? e0 : kNoHit, k1 = h1 ? e1 : kNoHit, k2 = h2 ? e2 : kNoHit, k3 = h3 ? e3 : kNoHit;
+                    uint32_t r0 = na.hi.z, r1 = na.hi.w, r2 = nb.hi.z, r3 = nb.hi.w;
+                    const int hits = (int)h0 + (int)h1 + (int)h2 + (int)h3;
+#define RT_CSWAP(ka, ra, kb, rb) { const bool sw = kb < ka; const float tk = sw ? ka : kb; ka = sw ? kb : ka; kb = tk; const uint32_t tr = sw ? ra : rb; ra = sw ? rb : ra; rb = tr; }
+                    RT_CSWAP(k0, r0, k1, r1) RT_CSWAP(k2, r2, k3, r3) RT_CSWAP(k0, r0, k2, r2) RT_CSWAP(k1, r1, k3, r3) RT_CSWAP(k1, r1, k2, r2)
+#undef RT_CSWAP
+                    if (hits > 3) { stack.push(sp, r3, k3); sp++; }
+                    if (hits > 2) { stack.push(sp, r2, k2); sp++; }
+                    if (hits > 1) { stack.push(sp, r1, k1); sp++; }
+                    if (hits > 0) {
+                        cur = r0;
+                    } else {
+                        float entry;
+                        do {
+                            if (sp == 0) { cur = kDoneRef; break; }
+                            sp--;
+                            stack.get(sp, cur, entry);
+                        } while (entry >= closest);
+                    }
+                } else {
+                    float d0, d1;
+                    bool h0, h1;
+                    uint2 q3;
+                    if (NODES == kNodesQ16) {  // one 32-byte record: 12 bounds on the 15-bit grid + the two child refs
+                        const Uint8 nq = ldg256u(qnodes + 2 * (size_t)cur);
+                        q3 = make_uint2(nq.hi.z, nq.hi.w);
+                        h0 = slab_q(nq.lo.x, nq.lo.y, nq.lo.z, qr, closest, d0);
+                        h1 = slab_q(nq.lo.w, nq.hi.x, nq.hi.y, qr, closest, d1);
+                    } else {
+                        const float4 *nd = nodes + 4 * (size_t)cur;
+                        // One 32-byte half per child (box + ref). Fetching the halves in opposite order on odd and even lanes
+                        // (to spread one LDG.256 over all four sector positions of the L1 lines) was measured: no gain, and
+                        // it makes tie-breaking lane-dependent, so every lane reads child 0 first.
+                        const Float8 na = ldg256(nd), nb = ldg256(nd + 2);
+                        q3 = make_uint2(__float_as_uint(na.hi.z), __float_as_uint(nb.hi.z));
+                        h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, so, inv, sg, closest, d0);
+                        h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, so, inv, sg, closest, d1);
+                    }
+#if RT_BRANCHFREE
+                    // one straight-line selection instead of four branch bodies (both / only 0 / only 1 / none): on incoherent
+                    // bounces each body ran with 4-15 of the warp's ~22 descending lanes (profiles/r2a: 12 % of the warp instructions)
+                    const bool zero_near = h0 && (!h1 || d0 < d1);  // child 0 is the one to enter
+                    const uint32_t near_ref = zero_near ? q3.x : q3.y;
+                    if (h0 && h1) {
+                        stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
+                        sp++;
+                    }
+                    if (h0 || h1) {
+                        cur = near_ref;
+                    } else {
+                        float entry;
+                        do {
+                            if (sp == 0) { cur = kDoneRef; break; }
+                            sp--;
+                            stack.get(sp, cur, entry);
+                        } while (entry >= closest);
+                    }
+#else
+                    if (h0 && h1) {
+                        const bool zero_near = d0 < d1;
+                        stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
+                        sp++;
+                        cur = zero_near ? q3.x : q3.y;
+                    } else if (h0) {
+                        cur = q3.x;
+                    } else if (h1) {
+                        cur = q3.y;
+                    } else {
+                        float entry;
+                        do {
+                            if (sp == 0) { cur = kDoneRef; break; }
+                            sp--;
+                            stack.get(sp, cur, entry);
+                        } while (entry >= closest);
+                    }
+#endif
+                }
+                // lanes that already hold a leaf wait at the loop exit: stop descending once only a few are left
+                if (__popc(__activemask()) < node_min) break;
+            }
+            }
+            __syncwarp();
+            const bool has_leaf = busy && (cur & kLeafBit) && cur != kDoneRef;
+            if (__any_sync(FULL, has_leaf)) leaf_phase_shared<STATS>(sc, has_leaf, cur, o, d, closest, prim, leaf_table + (threadIdx.x & ~31u), ctr);
+            if (has_leaf) {
+                float entry;  // pop, culling entries that can no longer beat the current hit (scene.cu:150-153)
+                do {
+                    if (sp == 0) { cur = kDoneRef; break; }
+                    sp--;
+                    stack.get(sp, cur, entry);
+                } while (entry >= closest);
+            }
+            if (busy && cur == kDoneRef) {
+                io.store(slot, closest, prim);
+                busy = false;
+            }
+            if ((uint32_t)__popc(__ballot_sync(FULL, busy)) < refill_below) break;
+        }
+#else
         // ---- walk: lanes leave individually, the warp reconverges at the __syncwarp below ----
         while (busy) {
             // descend through internal records until this lane holds a leaf (or runs dry)
@@ -466,6 +696,26 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
                         h0 = slab(na.lo.x, na.lo.y, na.lo.z, na.lo.w, na.hi.x, na.hi.y, so, inv, sg, closest, d0);
                         h1 = slab(nb.lo.x, nb.lo.y, nb.lo.z, nb.lo.w, nb.hi.x, nb.hi.y, so, inv, sg, closest, d1);
                     }
+#if RT_BRANCHFREE
+                    // one straight-line selection instead of four branch bodies (both / only 0 / only 1 / none): on incoherent
+                    // bounces each body ran with 4-15 of the warp's ~22 descending lanes (profiles/r2a: 12 % of the warp instructions)
+                    const bool zero_near = h0 && (!h1 || d0 < d1);  // child 0 is the one to enter
+                    const uint32_t near_ref = zero_near ? q3.x : q3.y;
+                    if (h0 && h1) {
+                        stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
+                        sp++;
+                    }
+                    if (h0 || h1) {
+                        cur = near_ref;
+                    } else {
+                        float entry;
+                        do {
+                            if (sp == 0) { cur = kDoneRef; break; }
+                            sp--;
+                            stack.get(sp, cur, entry);
+                        } while (entry >= closest);
+                    }
+#else
                     if (h0 && h1) {
                         const bool zero_near = d0 < d1;
                         stack.push(sp, zero_near ? q3.y : q3.x, zero_near ? d1 : d0);
@@ -483,6 +733,7 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
                             stack.get(sp, cur, entry);
                         } while (entry >= closest);
                     }
+#endif
                 }
                 // lanes that already hold a leaf wait at the loop exit: stop descending once only a few are left
                 if (__popc(__activemask()) < node_min) break;
@@ -506,6 +757,7 @@ __device__ __forceinline__ void trace_persistent(const DeviceScene &sc, uint32_t
             }
             if (__popc(__activemask()) < refill_below) break;  // heuristic only: correctness never depends on this mask
         }
+#endif
         __syncwarp();
     }
 }
