@@ -5,9 +5,9 @@
   torchrun ... bench.py --gpus N ...        (one rank per GPU, NCCL; launched by the driver for N > 1)
 
 A "step" is one whole frame of the workload: every pass of every bounce (generate -> closest hit -> shade -> compact
-[-> reorder]) plus, for N > 1, the NCCL reduce of the float accumulation buffer to rank 0. The frame's RAY SEQUENCE is
-split into equal contiguous shares across the ranks (rt_render_opts.ray_first / ray_count: whole passes when the pass
-count divides, partial passes otherwise; strong scaling: the frame is fixed). `value` = live ray-bounces
+[-> reorder]) plus, for N > 1, the NCCL reduce of the float accumulation buffer to rank 0. Every pixel's SAMPLES are
+split into equal shares across the ranks (rt_render_opts.sample_first / sample_count: whole passes when the pass count
+divides, a few samples of every pixel of one more pass otherwise; strong scaling: the frame is fixed). `value` = live ray-bounces
 of the whole frame / device time (CUDA events on the render stream, max over ranks). `e2e` is the same frame through the
 reference-facing call with HOST buffers: rt_scene_upload (H2D of the scene) + render + D2H of the sums, every step.
 
@@ -67,7 +67,7 @@ def config_for(args):
             "glass_teapot": " (synthetic env map: the asset is not in the checkout)"}.get(scene, "")
     return {"workload": f"{scene}.scene {w}x{h} {spp} spp {bounces} bounces{note}",
             "passes": (spp + PASS_SPP - 1) // PASS_SPP, "pass_spp": PASS_SPP, "sort": int(bool(args.sort)),
-            "parallelism": f"ray-sequence split x{args.gpus} + NCCL reduce",
+            "parallelism": f"per-pixel sample split x{args.gpus} + NCCL reduce",
             "l2": "inputs larger than L2: ray queues are %.1f GB per pass; the packed scene is L2-resident by nature" % (w * h * PASS_SPP * 40 * 2 / 1e9)}
 
 
@@ -264,17 +264,21 @@ def ref_gpu_timing(scene, w, h, bounces, lpp):
     return out
 
 
-def newest_ncu_summary():
-    """profiles/r*_traffic.json with the highest name (= the latest capture). None if there is none."""
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json")))
-    for f in reversed(files):
+def newest_ncu_summary(build=None):
+    """The ncu summary (profiles/r*_traffic.json, written by tools/ncu_summary.py) of THIS build if there is one, else the one
+    with the highest name (= the latest capture; bench.py then reports it as stale and leaves the derived keys out)."""
+    found = []
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json"))):
         try:
             d = json.load(open(f))
-            d["_file"] = os.path.relpath(f, ROOT)
-            return d
         except (OSError, ValueError):
             continue
-    return None
+        if "trace_rays_kernel" not in d or "build_id" not in d:
+            continue
+        d["_file"] = os.path.relpath(f, ROOT)
+        found.append(d)
+    same = [d for d in found if d.get("build_id") == build and "nodes=f32" in d.get("workload", "")]
+    return (same or found or [None])[-1]
 
 
 def main():
@@ -300,7 +304,7 @@ def main():
 
     import cuda_raytracer_b200 as rt
     from cuda_raytracer_b200.core import build_id
-    from cuda_raytracer_b200.multi_gpu import DeviceFramebuffer as _DevBuf, ray_range
+    from cuda_raytracer_b200.multi_gpu import DeviceFramebuffer as _DevBuf, sample_range
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the render core has no CPU fallback (use --impl reference for the CPU path)")
@@ -314,8 +318,8 @@ def main():
     scene = rt.load_scene(scene_name + ".scene", cwd=SCENES).set_image(w, h, spp, bounces)
     total_passes = (spp + PASS_SPP - 1) // PASS_SPP
     total_rays = w * h * spp
-    first, count = ray_range(total_rays, rank, world)
-    share = dict(ray_first=first, ray_count=count) if world > 1 else {}  # one GPU: the whole frame, no range
+    first, count = sample_range(spp, rank, world)
+    share = dict(sample_first=first, sample_count=count) if world > 1 else {}  # one GPU: the whole frame, no range
     sort = bool(args.sort)
 
     r = rt.Renderer(local_rank, nodes=args.nodes)
@@ -335,7 +339,7 @@ def main():
             st = r.last_stats
             dev_s, live, launches, tr_ms, sh_ms, so_ms = st.loop_seconds, st.live_ray_bounces, st.kernel_launches, st.trace_ms, st.shade_ms, st.sort_ms
         else:  # more ranks than rays: contribute zeros
-            ptr = r.render_device(sort=sort, ray_first=total_rays, ray_count=1)
+            ptr = r.render_device(sort=sort, sample_first=spp, sample_count=1)
             dev_s = live = launches = tr_ms = sh_ms = so_ms = 0
         red_s = 0.0
         if dist is not None:
@@ -360,7 +364,7 @@ def main():
         if dist is None:
             r.render(sort=sort, out=host_out.reshape(h, w, 3), pass_group=args.pass_group)
         else:
-            ptr = r.render_device(sort=sort, pass_group=args.pass_group, **(share if count > 0 else dict(ray_first=total_rays, ray_count=1)))
+            ptr = r.render_device(sort=sort, pass_group=args.pass_group, **(share if count > 0 else dict(sample_first=spp, sample_count=1)))
             fb = torch.as_tensor(_DevBuf(ptr, n_floats), device=f"cuda:{local_rank}")
             dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)
             if rank == 0:
@@ -470,7 +474,7 @@ def main():
                 "timing_note": "kernel durations: CUDA event pairs around every launch in %d attribution step(s) run right after the timed region "
                                "(one wave at a time, %.1f ms per step); the timed region itself runs two waves at a time on two streams, where "
                                "per-kernel intervals would overlap" % (args.steps, attr_s / args.steps * 1e3)}
-    ncu = newest_ncu_summary()
+    ncu = newest_ncu_summary(build_id())
     if ncu is not None:
         same_build = ncu.get("build_id") == build_id()
         roofline["ncu_source"] = {"file": ncu["_file"], "raw_csv": ncu.get("raw_csv"), "build_id": ncu.get("build_id"), "this_build_id": build_id(),

@@ -51,7 +51,7 @@ class RenderOpts(C.Structure):
     _fields_ = [("sort", C.c_int32), ("pass_spp", C.c_int32), ("pass_first", C.c_int32), ("pass_count", C.c_int32),
                 ("collect_stats", C.c_int32), ("stream_id", C.c_int32), ("sort_bits", C.c_int32), ("pass_group", C.c_int32),
                 ("kernel_timing", C.c_int32), ("root_start", C.c_int32), ("single_pipe", C.c_int32), ("reserved", C.c_int32),
-                ("ray_first", C.c_int64), ("ray_count", C.c_int64)]
+                ("ray_first", C.c_int64), ("ray_count", C.c_int64), ("sample_first", C.c_int32), ("sample_count", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -301,30 +301,32 @@ class Renderer:
 
     @staticmethod
     def _opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing=False, pass_group=0, root_start=False,
-              single_pipe=False, ray_first=0, ray_count=0):
+              single_pipe=False, ray_first=0, ray_count=0, sample_first=0, sample_count=0):
         return RenderOpts(1 if sort else 0, pass_spp, pass_first, pass_count, 1 if collect_stats else 0, stream_id, sort_bits,
-                          pass_group, 1 if timing else 0, 1 if root_start else 0, 1 if single_pipe else 0, 0, ray_first, ray_count)
+                          pass_group, 1 if timing else 0, 1 if root_start else 0, 1 if single_pipe else 0, 0, ray_first, ray_count,
+                          sample_first, sample_count)
 
     def render(self, sort=True, out=None, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0,
-               timing=False, pass_group=0, root_start=False, single_pipe=False, ray_first=0, ray_count=0):
+               timing=False, pass_group=0, root_start=False, single_pipe=False, ray_first=0, ray_count=0, sample_first=0, sample_count=0):
         """rt_render: host output (float32[H,W,3] un-normalised sums). ``out`` may be a preallocated (pinned) array.
         ``root_start`` makes primary rays walk from the BVH root instead of their tile's entry records (same results);
-        ``ray_first`` / ``ray_count`` (> 0) select a range of the frame's ray sequence instead of whole passes."""
+        ``ray_first`` / ``ray_count`` (> 0) select a range of the frame's ray sequence instead of whole passes,
+        ``sample_first`` / ``sample_count`` (> 0) a range of every pixel's samples (the multi-GPU split)."""
         if out is None:
             out = np.empty((self.height, self.width, 3), np.float32)
         assert out.dtype == np.float32 and out.size == self.width * self.height * 3 and out.flags.c_contiguous
         o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group, root_start,
-                       single_pipe, ray_first, ray_count)
+                       single_pipe, ray_first, ray_count, sample_first, sample_count)
         st = Stats()
         _check(lib().rt_render(self._ctx, C.byref(o), out.ctypes.data, C.byref(st)), self._ctx)
         self.last_stats = st
         return out
 
     def render_device(self, sort=True, pass_spp=0, pass_first=0, pass_count=0, collect_stats=False, stream_id=0, sort_bits=0,
-                      timing=False, pass_group=0, root_start=False, single_pipe=False, ray_first=0, ray_count=0):
+                      timing=False, pass_group=0, root_start=False, single_pipe=False, ray_first=0, ray_count=0, sample_first=0, sample_count=0):
         """rt_render_device: returns the device pointer (int) of the float32[H*W*3] framebuffer."""
         o = self._opts(sort, pass_spp, pass_first, pass_count, collect_stats, stream_id, sort_bits, timing, pass_group, root_start,
-                       single_pipe, ray_first, ray_count)
+                       single_pipe, ray_first, ray_count, sample_first, sample_count)
         st = Stats()
         ptr = C.c_void_p()
         _check(lib().rt_render_device(self._ctx, C.byref(o), C.byref(ptr), C.byref(st)), self._ctx)
@@ -443,7 +445,8 @@ class MultiRenderer:
             out = np.empty((self.height, self.width, 3), np.float32)
         o = Renderer._opts(sort, kw.pop("pass_spp", 0), kw.pop("pass_first", 0), kw.pop("pass_count", 0), kw.pop("collect_stats", False),
                            kw.pop("stream_id", 0), kw.pop("sort_bits", 0), kw.pop("timing", False), kw.pop("pass_group", 0),
-                           kw.pop("root_start", False), kw.pop("single_pipe", False), kw.pop("ray_first", 0), kw.pop("ray_count", 0))
+                           kw.pop("root_start", False), kw.pop("single_pipe", False), kw.pop("ray_first", 0), kw.pop("ray_count", 0),
+                           kw.pop("sample_first", 0), kw.pop("sample_count", 0))
         assert not kw, f"unknown options {sorted(kw)}"
         st = Stats()
         self._check(lib().rt_multi_render(self._m, C.byref(o), out.ctypes.data if want_host else None, C.byref(st)))

@@ -134,6 +134,9 @@ struct BounceArgs {
     uint32_t n_first;       // rays of the wave = group x pass_rays (bounce 0 only)
     uint32_t pass_rays;     // rays of ONE pass (pixels x rays_per_pixel); ray id = pass-in-wave x pass_rays + index in pass
     uint32_t ray_offset;    // a wave that holds PART of one pass (rt_render_opts.ray_first / ray_count): index in pass = id + ray_offset
+    uint32_t sub_count;     // > 0: the wave holds samples [sub_first, sub_first + sub_count) of EVERY pixel of one pass
+    uint32_t sub_first;     //      (rt_render_opts.sample_first / sample_count): index in pass = (id / sub_count) * rays_per_pixel + sub_first + id % sub_count
+    FastDiv div_sub_count;
     int32_t bounce;
     int32_t rays_per_pixel; // of every pass of this wave
     FastDiv div_pass_rays, div_rays_per_pixel;

@@ -28,6 +28,15 @@ constexpr int kBlocksPerSMLocal = RT_TRACE_CTAS;  // tracer: 8 CTAs -> 32 warps 
 
 __device__ __forceinline__ uint32_t lanemask_lt() { return (1u << (threadIdx.x & 31)) - 1u; }
 
+// Ray index INSIDE ITS PASS (what the reference's seeds and pixel are functions of: raytracing.cu:89, scene.cu:81,83) of the
+// ray with number j inside the wave's pass: j itself for whole passes, shifted for a ray range, strided for a sample range.
+__device__ __forceinline__ uint32_t pass_index(const BounceArgs &a, uint32_t j)
+{
+    if (a.sub_count == 0u) return j + a.ray_offset;
+    const uint32_t px = fast_div(j, a.div_sub_count);
+    return px * (uint32_t)a.rays_per_pixel + a.sub_first + (j - px * a.sub_count);
+}
+
 // Warp-aggregated accumulation: consecutive queue positions often belong to the same pixel (rays_per_pixel samples in a
 // row at bounce 0; later the compaction keeps a pixel's survivors of one octant together), so each maximal run of equal pixels inside the warp is summed with
 // shuffles and only its first lane issues the atomics. Must be called by all 32 lanes.
@@ -68,7 +77,7 @@ struct QueueTraceIO {
     {
         if (FIRST) {
             const uint32_t g = fast_div(i, a.div_pass_rays);  // pass of the wave; seeds and pixel follow the index inside that pass
-            if (!generate_ray(sc, i - g * a.pass_rays + a.ray_offset, a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d)) return false;
+            if (!generate_ray(sc, pass_index(a, i - g * a.pass_rays), a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d)) return false;
         } else {
             const uint32_t slot = a.order ? __ldg(a.order + i) : i;
             const float4 ra = __ldcs(a.in.qa + slot), rb = __ldcs(a.in.qb + slot);
@@ -91,7 +100,7 @@ struct QueueTraceIO {
         cur = 0;
         if (!FIRST || !use_entries) return;
         const uint32_t g = fast_div(i, a.div_pass_rays);
-        const uint32_t pixel = fast_div(i - g * a.pass_rays + a.ray_offset, a.div_rays_per_pixel);
+        const uint32_t pixel = fast_div(pass_index(a, i - g * a.pass_rays), a.div_rays_per_pixel);
         const uint32_t y = fast_div(pixel, sc.div_width), x = pixel - y * (uint32_t)sc.width;
         const uint4 *rec = a.entry_lists + 4 * (size_t)((y / kEntryTile) * (uint32_t)a.entry_tiles_x + x / kEntryTile);
         const uint4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2), q3 = __ldg(rec + 3);
@@ -209,7 +218,7 @@ __global__ void RT_SHADE_BOUNDS shade_kernel(const DeviceScene sc, const BounceA
         if (active) {
             if (FIRST) {
                 const uint32_t g = fast_div(id, a.div_pass_rays);
-                active = generate_ray(sc, id - g * a.pass_rays + a.ray_offset, a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d);
+                active = generate_ray(sc, pass_index(a, id - g * a.pass_rays), a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d);
             } else {
                 o = f3(cur.ra.x, cur.ra.y, cur.ra.z);
                 d = f3(cur.ra.w, cur.rb.x, cur.rb.y);
@@ -224,7 +233,7 @@ __global__ void RT_SHADE_BOUNDS shade_kernel(const DeviceScene sc, const BounceA
             const float2 h = cur.h;
             const float closest = h.x;
             const int prim = __float_as_int(h.y);
-            const uint32_t g = fast_div(id, a.div_pass_rays), index = id - g * a.pass_rays + a.ray_offset;  // pass of the wave, ray index inside it
+            const uint32_t g = fast_div(id, a.div_pass_rays), index = pass_index(a, id - g * a.pass_rays);  // pass of the wave, ray index inside it
             pixel = fast_div(index, a.div_rays_per_pixel);
             if (prim < 0) {
                 radiance = shade_miss(sc, d) * T;

@@ -1,12 +1,13 @@
-// Several GPUs of one box behind the C ABI (rt_multi_*, include/rt_core.h): the scene is replicated, the frame's ray
-// sequence is cut into equal contiguous shares (one per device, rt_render_opts.ray_first / ray_count), every device renders
+// Several GPUs of one box behind the C ABI (rt_multi_*, include/rt_core.h): the scene is replicated, every pixel's samples
+// are cut into equal shares (one per device, rt_render_opts.sample_first / sample_count), every device renders
 // its share from its own host thread, and the float accumulation buffers are summed into device 0's with ONE ncclReduce
 // over NVLink (the reference's gpu_raytrace, raytracing.cu:170-284, is single-GPU). Included by rt_core.cu.
 //
 // NCCL is loaded at run time (dlopen "libnccl.so.2"): the single-GPU library has no NCCL dependency, and inside a process
 // that already holds a copy (torch bundles one) the same copy is used. When the device list names one device more than
 // once (a box with fewer GPUs than shares: the round-end test box has one) NCCL cannot form the communicator; the sum is
-// then a plain add kernel on device 0, which reads the other contexts' buffers directly (same device).
+// then a plain add kernel on device 0, which reads the other contexts' buffers directly (same device). The same kernels over
+// peer access replace NCCL when RT_MULTI_REDUCE=p2p is set (front-end word reduce=p2p): no communicator start-up.
 #pragma once
 
 #include <dlfcn.h>
@@ -122,7 +123,12 @@ extern "C" int rt_multi_create(rt_multi **out, const int *devices, int n)
         rt_multi_destroy(m);
         return mfail(nullptr, RT_ERR_CUDA, "rt_multi_create: event creation failed");
     }
-    if (n > 1 && distinct) {
+    // RT_MULTI_REDUCE=p2p: sum the buffers with add kernels on device 0 that read the peers' memory over NVLink (peer access)
+    // instead of NCCL. For one-shot use (the command line): ncclCommInitAll + the first collective took ~3.3 s on an 8-GPU box
+    // (GPU Took 4.27 s for a 0.48 s loop), more than a whole 4K frame. NCCL stays the default (the reduce itself is 0.8 ms).
+    const char *reduce_env = std::getenv("RT_MULTI_REDUCE");
+    const bool p2p = reduce_env && std::strcmp(reduce_env, "p2p") == 0;
+    if (n > 1 && distinct && !p2p) {
         if (!m->nccl.load()) { rt_multi_destroy(m); return mfail(nullptr, RT_ERR_CUDA, "rt_multi_create: libnccl.so.2 not found (needed to combine the devices' framebuffers)"); }
         m->comms.assign((size_t)n, nullptr);
         const int r = m->nccl.comm_init_all(m->comms.data(), n, devices);
@@ -133,10 +139,18 @@ extern "C" int rt_multi_create(rt_multi **out, const int *devices, int n)
             return mfail(nullptr, RT_ERR_CUDA, msg);
         }
         m->use_nccl = true;
-    } else if (n > 1) {  // repeated devices: contexts 1.. hand their buffers to context 0's add kernel
+    } else if (n > 1) {  // contexts 1.. hand their buffers to context 0's add kernel: one device named several times, or peers
         m->ev_done.assign((size_t)n, nullptr);
         for (int i = 0; i < n; i++) {
-            if (devices[i] != devices[0]) { rt_multi_destroy(m); return mfail(nullptr, RT_ERR_INVALID, "rt_multi_create: a device list with repeats must name one device only"); }
+            if (!distinct && devices[i] != devices[0]) { rt_multi_destroy(m); return mfail(nullptr, RT_ERR_INVALID, "rt_multi_create: a device list with repeats must name one device only"); }
+            if (distinct && i > 0) {
+                int can = 0;
+                cudaSetDevice(devices[0]);
+                cudaDeviceCanAccessPeer(&can, devices[0], devices[i]);
+                const cudaError_t e = can ? cudaDeviceEnablePeerAccess(devices[i], 0) : cudaErrorPeerAccessUnsupported;
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) { rt_multi_destroy(m); return mfail(nullptr, RT_ERR_CUDA, "rt_multi_create: RT_MULTI_REDUCE=p2p needs peer access from the first device to every other"); }
+                cudaGetLastError();
+            }
             cudaSetDevice(devices[i]);
             cudaEventCreateWithFlags(&m->ev_done[i], cudaEventDisableTiming);
         }
@@ -176,27 +190,39 @@ extern "C" int rt_multi_render(rt_multi *m, const rt_render_opts *opts_in, float
     rt_render_opts base{};
     if (opts_in) base = *opts_in;
     base.sort = opts_in ? opts_in->sort : 1;
-    // the rays this call covers (a pass range or ray range of the caller's is honoured), cut into n equal shares
+    // What this call covers, cut into n equal shares. Default (and with a sample range of the caller's): SAMPLES of every pixel,
+    // so that each share spans the whole image and equal shares cost the same. A pass range or ray range of the caller's is
+    // honoured as a range of the ray sequence.
     const int pass_spp = base.pass_spp > 0 ? base.pass_spp : 20;
     const int64_t pixels = (int64_t)c0->ds.width * c0->ds.height;
     const int total_passes = (c0->ray_count + pass_spp - 1) / pass_spp;
-    int64_t first = 0, count = pixels * c0->ray_count;
-    if (base.ray_count > 0) {
-        first = std::max<int64_t>(0, base.ray_first);
-        count = std::max<int64_t>(0, std::min(first + base.ray_count, pixels * c0->ray_count) - first);
-    } else if (base.pass_first > 0 || base.pass_count > 0) {
-        const int p0 = std::min(std::max(0, base.pass_first), total_passes);
-        const int p1 = base.pass_count > 0 ? std::min(total_passes, p0 + base.pass_count) : total_passes;
-        first = pixels * std::min<int64_t>((int64_t)p0 * pass_spp, c0->ray_count);
-        count = pixels * std::min<int64_t>((int64_t)p1 * pass_spp, c0->ray_count) - first;
+    const bool by_rays = base.sample_count <= 0 && (base.ray_count > 0 || base.pass_first > 0 || base.pass_count > 0);
+    int64_t first = 0, count = c0->ray_count, past_end = c0->ray_count;  // in samples per pixel, or in rays
+    if (by_rays) {
+        count = past_end = pixels * c0->ray_count;
+        if (base.ray_count > 0) {
+            first = std::max<int64_t>(0, base.ray_first);
+            count = std::max<int64_t>(0, std::min(first + base.ray_count, past_end) - first);
+        } else {
+            const int p0 = std::min(std::max(0, base.pass_first), total_passes);
+            const int p1 = base.pass_count > 0 ? std::min(total_passes, p0 + base.pass_count) : total_passes;
+            first = pixels * std::min<int64_t>((int64_t)p0 * pass_spp, c0->ray_count);
+            count = pixels * std::min<int64_t>((int64_t)p1 * pass_spp, c0->ray_count) - first;
+        }
+    } else if (base.sample_count > 0) {
+        first = std::max(0, base.sample_first);
+        count = std::max<int64_t>(0, std::min<int64_t>(first + base.sample_count, c0->ray_count) - first);
     }
     std::vector<rt_stats> st((size_t)n);
     int rc = for_each_device(m, [&](int i) {
         rt_render_opts o = base;
         const int64_t lo = first + count * i / n, hi = first + count * (i + 1) / n;
         o.pass_first = o.pass_count = 0;
-        o.ray_first = hi > lo ? lo : pixels * (int64_t)c0->ray_count;  // an empty share: a range past the end renders nothing
-        o.ray_count = std::max<int64_t>(1, hi - lo);
+        o.ray_first = o.ray_count = 0;
+        o.sample_first = o.sample_count = 0;
+        // an empty share: a range past the end renders nothing and leaves a cleared framebuffer
+        if (by_rays) { o.ray_first = hi > lo ? lo : past_end; o.ray_count = std::max<int64_t>(1, hi - lo); }
+        else { o.sample_first = (int32_t)(hi > lo ? lo : past_end); o.sample_count = (int32_t)std::max<int64_t>(1, hi - lo); }
         int r = render_impl(m->ctx[i], &o, &st[i]);
         if (r == RT_OK && !m->ev_done.empty()) {
             cudaSetDevice(m->ctx[i]->device);

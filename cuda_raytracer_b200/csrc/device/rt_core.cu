@@ -860,26 +860,37 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     // the pass and the ray's index inside it: raytracing.cu:89,229,236, scene.cu:81).
     struct Segment {
         int pass;
-        uint32_t offset, count;
+        uint32_t offset, count;         // rays [offset, offset + count) of the pass; strided: count = pixels x sub_count
+        uint32_t sub_first, sub_count;  // sub_count > 0: samples [sub_first, sub_first + sub_count) of every pixel
     };
     std::vector<Segment> segs;
     auto spp_of = [&](int p) { return std::min(ctx->ray_count - p * pass_spp, pass_spp); };
-    if (opts.ray_count > 0) {
+    if (opts.sample_count > 0) {  // samples [s0, s1) of every pixel: pass p holds samples [p * pass_spp, p * pass_spp + spp_of(p))
+        if (opts.sample_first < 0) return fail(ctx, RT_ERR_INVALID, "rt_render: sample_first must be >= 0");
+        const int64_t s0 = opts.sample_first, s1 = std::min<int64_t>((int64_t)opts.sample_first + opts.sample_count, ctx->ray_count);
+        for (int p = 0; p < total_passes; p++) {
+            const int64_t lo = std::max<int64_t>(s0, (int64_t)p * pass_spp), hi = std::min<int64_t>(s1, (int64_t)p * pass_spp + spp_of(p));
+            if (hi <= lo) continue;
+            const uint32_t k0 = (uint32_t)(lo - (int64_t)p * pass_spp), m = (uint32_t)(hi - lo);
+            if ((int)m == spp_of(p)) segs.push_back(Segment{p, 0u, (uint32_t)(pixels * (size_t)m), 0u, 0u});
+            else segs.push_back(Segment{p, 0u, (uint32_t)(pixels * (size_t)m), k0, m});
+        }
+    } else if (opts.ray_count > 0) {
         if (opts.ray_first < 0) return fail(ctx, RT_ERR_INVALID, "rt_render: ray_first must be >= 0");
         int64_t start = 0;
         const int64_t u0 = opts.ray_first, u1 = opts.ray_first + opts.ray_count;
         for (int p = 0; p < total_passes && start < u1; p++) {
             const int64_t n = (int64_t)pixels * spp_of(p);
-            const int64_t a = std::max(u0, start), b = std::min(u1, start + n);
-            if (b > a) segs.push_back(Segment{p, (uint32_t)(a - start), (uint32_t)(b - a)});
+            const int64_t lo = std::max(u0, start), hi = std::min(u1, start + n);
+            if (hi > lo) segs.push_back(Segment{p, (uint32_t)(lo - start), (uint32_t)(hi - lo), 0u, 0u});
             start += n;
         }
     } else {
         const int pass_first = std::max(0, opts.pass_first);
         const int pass_end = opts.pass_count > 0 ? std::min(total_passes, pass_first + opts.pass_count) : total_passes;
-        for (int p = pass_first; p < pass_end; p++) segs.push_back(Segment{p, 0u, (uint32_t)(pixels * (size_t)spp_of(p))});
+        for (int p = pass_first; p < pass_end; p++) segs.push_back(Segment{p, 0u, (uint32_t)(pixels * (size_t)spp_of(p)), 0u, 0u});
     }
-    auto whole = [&](const Segment &g) { return g.offset == 0 && (size_t)g.count == pixels * (size_t)spp_of(g.pass); };
+    auto whole = [&](const Segment &g) { return g.sub_count == 0 && g.offset == 0 && (size_t)g.count == pixels * (size_t)spp_of(g.pass); };
     const int n_segs = (int)segs.size();
     const bool collect = opts.collect_stats != 0;
     const bool timing = opts.kernel_timing != 0;  // CUDA-event pair around every bounce kernel and every reorder pass
@@ -1014,6 +1025,9 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             a.n_first = total;
             a.pass_rays = pass_rays;
             a.ray_offset = partial ? segs[si].offset : 0u;
+            a.sub_count = partial ? segs[si].sub_count : 0u;
+            a.sub_first = partial ? segs[si].sub_first : 0u;
+            a.div_sub_count = make_fast_div(std::max(1u, a.sub_count));
             a.bounce = b;
             a.rays_per_pixel = rays_to_cast;
             a.div_pass_rays = make_fast_div(pass_rays);

@@ -3,7 +3,7 @@
 // stdout lines and ./raytracing.png output. The render itself goes through the C ABI (rt_core.h); there is no CPU
 // renderer in this product, so `cpu` without a GPU path is refused with exit code 2 like "no hardware".
 // Extra words the reference would ignore: out=<path>, stats, no_bloom, device=<n>, gpus=<n> (split the frame's rays over the first
-// n GPUs, one NCCL reduce), host_bvh (build the BVH on the host as the reference does; the default is the same binned-SAH
+// n GPUs, one NCCL reduce; reduce=p2p sums over peer access instead), host_bvh (build the BVH on the host as the reference does; the default is the same binned-SAH
 // build on the device, ~70x faster), gpu_bvh (the default, kept for old command lines), sbvh (host tree with spatial splits).
 #include <algorithm>
 #include <chrono>
@@ -36,6 +36,7 @@ int main(int argc, char **argv)
         else if (!std::strcmp(w, "host_bvh")) gpu_bvh = false;
         else if (!std::strcmp(w, "sbvh")) { sbvh = true; gpu_bvh = false; }
         else if (!std::strncmp(w, "gpus=", 5)) gpus = std::max(1, std::atoi(w + 5));
+        else if (!std::strcmp(w, "reduce=p2p")) setenv("RT_MULTI_REDUCE", "p2p", 1);  // peer-access add kernels instead of NCCL (no ~3 s start-up)
         else if (!std::strncmp(w, "out=", 4)) out_path = w + 4;
         else if (!std::strncmp(w, "device=", 7)) device = std::atoi(w + 7);
     }

@@ -27,7 +27,7 @@
 extern "C" {
 #endif
 
-#define RT_API_VERSION 6
+#define RT_API_VERSION 7
 
 typedef enum rt_status {
     RT_OK = 0,
@@ -92,7 +92,11 @@ typedef struct rt_render_opts {
     int64_t ray_count;     /* (pass 0's rays, then pass 1's, ...; a pass holds width*height*spp_of_that_pass rays, pixel-major) and
                               ignore pass_first / pass_count. A ray's seeds depend on its pass and its index inside the pass
                               (raytracing.cu:89,229,236, scene.cu:81), so disjoint ranges add up to the whole frame exactly as
-                              disjoint pass ranges do; used for the per-GPU split when the pass count does not divide. */
+                              disjoint pass ranges do. */
+    int32_t sample_first;  /* with sample_count > 0: render only samples [sample_first, sample_first + sample_count) of EVERY pixel */
+    int32_t sample_count;  /* (sample s of a pixel is ray s % pass_spp of that pixel in pass s / pass_spp) and ignore the pass and ray
+                              ranges. This is the per-GPU split: every share covers the whole image, so shares of equal size cost
+                              the same whatever the picture shows (a ray range of a pass covers a band of rows: sky or geometry). */
 } rt_render_opts;
 
 typedef struct rt_stats {

@@ -94,6 +94,7 @@ def port():
         L.oracle_process.argtypes = [S, f32p, u32p, C.c_int]
         L.oracle_render.argtypes = [S, C.c_int, C.c_int, C.c_int, f32p, C.POINTER(Counters)]
         L.oracle_render_select.argtypes = [S, C.c_int, C.c_int, C.c_int, C.c_int64, C.c_int64, C.c_void_p, f32p, C.POINTER(Counters)]
+        L.oracle_render_samples.argtypes = [S, C.c_int, C.c_int, C.c_int, f32p, C.POINTER(Counters)]
         L.oracle_sort_key.argtypes = [S, f32p, f32p, f32p]
         L.oracle_sort_key.restype = C.c_uint32
         L.oracle_bloom.argtypes = [f32p, C.c_int, C.c_int, C.c_int]

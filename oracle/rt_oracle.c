@@ -397,8 +397,24 @@ void oracle_render(const oracle_scene *s, int seed_mode, int pass_first, int pas
  * the whole frame. Selection = passes [pass_first, pass_first + pass_count) (pass_count < 0: all), AND rays
  * [ray_first, ray_first + ray_count) of the frame's ray sequence (pass 0's rays, then pass 1's, ...; ray_count < 0: all),
  * AND pixels inside window = {x0, y0, w, h} (NULL: the whole image). out_rgb is the full-size image. */
+static void render_subset(const oracle_scene *s, int seed_mode, int pass_first, int pass_count, int64_t ray_first, int64_t ray_count,
+                          const int32_t *window, int sample_first, int sample_count, float *out_rgb, oracle_counters *counters);
+
 void oracle_render_select(const oracle_scene *s, int seed_mode, int pass_first, int pass_count, int64_t ray_first, int64_t ray_count,
                           const int32_t *window, float *out_rgb, oracle_counters *counters)
+{
+    render_subset(s, seed_mode, pass_first, pass_count, ray_first, ray_count, window, 0, -1, out_rgb, counters);
+}
+
+/* Samples [sample_first, sample_first + sample_count) of EVERY pixel (sample i of a pixel = ray i % 20 of that pixel in pass
+ * i / 20): the subset one GPU renders in the multi-GPU split. */
+void oracle_render_samples(const oracle_scene *s, int seed_mode, int sample_first, int sample_count, float *out_rgb, oracle_counters *counters)
+{
+    render_subset(s, seed_mode, 0, -1, 0, -1, NULL, sample_first, sample_count, out_rgb, counters);
+}
+
+static void render_subset(const oracle_scene *s, int seed_mode, int pass_first, int pass_count, int64_t ray_first, int64_t ray_count,
+                          const int32_t *window, int sample_first, int sample_count, float *out_rgb, oracle_counters *counters)
 {
     int pixel_count = s->width * s->height;
     memset(out_rgb, 0, sizeof(float) * 3 * (size_t)pixel_count);
@@ -423,14 +439,25 @@ void oracle_render_select(const oracle_scene *s, int seed_mode, int pass_first, 
             hi = ray_first + ray_count - pass_start < total_rays ? ray_first + ray_count - pass_start : total_rays;
         }
         if (hi <= lo) continue;
+        /* samples of this pass inside the sample range: k in [k0, k1) */
+        int k0 = 0, k1 = rays_to_cast;
+        if (sample_count >= 0) {
+            int pass_s0 = this_pass * ORACLE_PER_PASS;
+            k0 = sample_first - pass_s0 > 0 ? sample_first - pass_s0 : 0;
+            k1 = sample_first + sample_count - pass_s0 < rays_to_cast ? sample_first + sample_count - pass_s0 : rays_to_cast;
+            if (k1 <= k0) continue;
+        }
+        const int32_t whole_image[4] = {0, 0, s->width, s->height};
+        const int32_t *win = window;  /* per pass: a partial sample range is enumerated pixel by pixel over the whole image */
+        if (!win && (k0 > 0 || k1 < rays_to_cast)) win = whole_image;
         /* the selected ray indices of this pass */
         size_t n_sel = 0;
-        if (window) {
-            size_t bound = (size_t)window[2] * window[3] * rays_to_cast;
+        if (win) {
+            size_t bound = (size_t)win[2] * win[3] * rays_to_cast;
             if (bound > cap) { cap = bound; ids = (int32_t *)realloc(ids, sizeof(int32_t) * cap); ray_data = (float *)realloc(ray_data, sizeof(float) * 12 * cap); }
-            for (int y = window[1]; y < window[1] + window[3]; y++)
-                for (int x = window[0]; x < window[0] + window[2]; x++)
-                    for (int k = 0; k < rays_to_cast; k++) {
+            for (int y = win[1]; y < win[1] + win[3]; y++)
+                for (int x = win[0]; x < win[0] + win[2]; x++)
+                    for (int k = k0; k < k1; k++) {
                         int64_t i = ((int64_t)y * s->width + x) * rays_to_cast + k;
                         if (i >= lo && i < hi) ids[n_sel++] = (int32_t)i;
                     }

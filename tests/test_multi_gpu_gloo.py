@@ -44,6 +44,15 @@ def test_ray_range_partitions_every_ray_once():
         mg.ray_range(10, 3, 3)
 
 
+def test_sample_range_partitions_every_sample_once():
+    for spp in (0, 1, 7, 20, 640, 1000, 1001):
+        for world in (1, 2, 3, 8, 64):
+            spans = [mg.sample_range(spp, r, world) for r in range(world)]
+            assert [s for f, c in spans for s in range(f, f + c)] == list(range(spp))
+            assert max(c for _, c in spans) - min(c for _, c in spans) <= 1
+    assert [mg.sample_range(1000, r, 8) for r in range(8)] == [(125 * r, 125) for r in range(8)]  # teapot as shipped on 8 GPUs
+
+
 def _worker(rank, world, port, out_path):
     here = os.path.dirname(os.path.abspath(__file__))
     root = os.path.dirname(here)
@@ -53,7 +62,7 @@ def _worker(rank, world, port, out_path):
     import torch
     import torch.distributed as dist
 
-    from util import load, oracle_arrays, oracle_render, oracle_render_select
+    from util import load, oracle_arrays, oracle_render, oracle_render_samples, oracle_render_select
 
     dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
     try:
@@ -68,13 +77,19 @@ def _worker(rank, world, port, out_path):
         rf, rc = mg.ray_range(A.width * A.height * A.ray_count, rank, world)
         part2, ctr = oracle_render_select(A, 1, ray_first=rf, ray_count=rc)
         t2 = torch.from_numpy(part2.reshape(-1).copy())
-        live = torch.tensor([ctr.live_ray_bounces], dtype=torch.int64)
+        # the product's split: an equal share of every pixel's samples (70 samples on 3 ranks: 24 / 23 / 23)
+        sf, sc = mg.sample_range(A.ray_count, rank, world)
+        part3, ctr3 = oracle_render_samples(A, sf, sc)
+        t3 = torch.from_numpy(part3.reshape(-1).copy())
+        live = torch.tensor([ctr.live_ray_bounces, ctr3.live_ray_bounces], dtype=torch.int64)
         mg.reduce_to_root(t2, dist, 0)
+        mg.reduce_to_root(t3, dist, 0)
         dist.reduce(live, dst=0, op=dist.ReduceOp.SUM)
         if rank == 0:
             whole, cw = oracle_render(A, 1)
-            np.savez(out_path, combined=t.numpy().reshape(whole.shape), combined_rays=t2.numpy().reshape(whole.shape), whole=whole,
-                     live=np.array([int(live[0]), cw.live_ray_bounces]))
+            np.savez(out_path, combined=t.numpy().reshape(whole.shape), combined_rays=t2.numpy().reshape(whole.shape),
+                     combined_samples=t3.numpy().reshape(whole.shape), whole=whole,
+                     live=np.array([int(live[0]), int(live[1]), cw.live_ray_bounces]))
     finally:
         dist.destroy_process_group()
 
@@ -92,5 +107,6 @@ def test_two_rank_split_equals_whole_frame(tmp_path, world):
     z = np.load(out)
     assert np.allclose(z["combined"], z["whole"], rtol=1e-5, atol=1e-5 * float(z["whole"].mean()))
     assert np.allclose(z["combined_rays"], z["whole"], rtol=1e-5, atol=1e-5 * float(z["whole"].mean()))
-    assert z["live"][0] == z["live"][1]
+    assert np.allclose(z["combined_samples"], z["whole"], rtol=1e-5, atol=1e-5 * float(z["whole"].mean()))
+    assert z["live"][0] == z["live"][2] and z["live"][1] == z["live"][2]
     assert z["whole"].mean() > 0

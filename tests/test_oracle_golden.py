@@ -188,6 +188,16 @@ def test_render_select_subsets_add_up():
     one, _ = oracle_render_select(A, 1, pass_first=1, pass_count=1)
     ref, _ = oracle_render(A, 1, 1, 1)
     assert one.tobytes() == ref.tobytes()
+    # sample ranges of every pixel (the multi-GPU split): 50 samples cut at 0 | 7 | 20 | 33 | 50 add up, counters included;
+    # samples [20, 40) are exactly pass 1
+    from util import oracle_render_samples
+    acc, live = np.zeros_like(whole, dtype=np.float64), 0
+    for a, b in ((0, 7), (7, 20), (20, 33), (33, 50)):
+        img, c = oracle_render_samples(A, a, b - a)
+        acc += img
+        live += c.live_ray_bounces
+    assert live == cw.live_ray_bounces and np.allclose(acc, whole, rtol=1e-5, atol=1e-6)
+    assert oracle_render_samples(A, 20, 20)[0].tobytes() == ref.tobytes()
 
 
 def test_sort_key_degenerate_as_in_reference():

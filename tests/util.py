@@ -78,6 +78,15 @@ def oracle_render_select(arrays, seed_mode=1, pass_first=0, pass_count=-1, ray_f
     return img, c
 
 
+def oracle_render_samples(arrays, sample_first, sample_count, seed_mode=1):
+    """The oracle's pass loop over samples [sample_first, sample_first + sample_count) of every pixel."""
+    S = arrays.oracle_struct()
+    img = np.zeros((arrays.height, arrays.width, 3), np.float32)
+    c = po.Counters()
+    po.port().oracle_render_samples(C.byref(S), seed_mode, int(sample_first), int(sample_count), img.reshape(-1), C.byref(c))
+    return img, c
+
+
 def scene_diag(arrays):
     """Diagonal of the triangle root box (1.0 when there are no triangles)."""
     if not len(arrays.triangles):
