@@ -74,7 +74,7 @@ EXPORTS = [
     # rt_core.h
     "rt_api_version", "rt_device_count", "rt_host_pin", "rt_host_unpin", "rt_create", "rt_set_node_mode", "rt_get_node_mode", "rt_destroy", "rt_last_error", "rt_scene_upload", "rt_scene_set_image",
     "rt_render", "rt_render_device", "rt_postprocess", "rt_framebuffer_upload", "rt_trace_closest", "rt_generate_rays",
-    "rt_process_rays", "rt_sort_pairs", "rt_scene_download_bvh", "rt_scene_bvh_device_ms", "rt_sort_device_ms", "rt_index_divide",
+    "rt_process_rays", "rt_sort_pairs", "rt_sort_pairs_static", "rt_scene_download_bvh", "rt_scene_bvh_device_ms", "rt_sort_device_ms", "rt_index_divide",
     "rt_probe_copy_gbs",
     "rt_multi_create", "rt_multi_destroy", "rt_multi_device_count", "rt_multi_last_error", "rt_multi_context", "rt_multi_set_node_mode",
     "rt_multi_scene_upload", "rt_multi_render", "rt_multi_reduce_ms", "rt_multi_postprocess",
@@ -116,6 +116,7 @@ def lib():
     L.rt_generate_rays.argtypes = [vp, i32, i32, i32, i32, vp]
     L.rt_process_rays.argtypes = [vp, vp, vp, i32]
     L.rt_sort_pairs.argtypes = [vp, vp, vp, i32, i32]
+    L.rt_sort_pairs_static.argtypes = [vp, vp, vp, vp, vp, i32, i32]
     L.rt_scene_download_bvh.argtypes = [vp, vp, i32, C.POINTER(i32), vp, i32]
     L.rt_scene_bvh_device_ms.argtypes = [vp]
     L.rt_scene_bvh_device_ms.restype = C.c_double
@@ -391,6 +392,11 @@ class Renderer:
     def sort_device_ms(self):
         return lib().rt_sort_device_ms(self._ctx)
 
+    def sort_pairs_static(self, d_keys_in, d_values_in, d_keys_out, d_values_out, n, bits=32):
+        """rt_sort_pairs_static: the same sort on DEVICE pointers (ints) with all scratch in the library's static device array:
+        no allocation, n <= SORT_STATIC_MAX_PAIRS. Calls on one device must not overlap."""
+        _check(lib().rt_sort_pairs_static(self._ctx, int(d_keys_in), int(d_values_in), int(d_keys_out), int(d_values_out), int(n), int(bits)), self._ctx)
+
     def sort_pairs(self, keys, values, bits=32):
         k = np.ascontiguousarray(keys, np.uint32).copy()
         v = np.ascontiguousarray(values, np.uint32).copy()
@@ -462,6 +468,9 @@ class MultiRenderer:
         b = np.empty((self.height, self.width, 3), np.uint8) if want_rgb8 else None
         self._check(lib().rt_multi_postprocess(self._m, 1 if bloom else 0, s.ctypes.data if want_sum else None, b.ctypes.data if want_rgb8 else None))
         return s, b
+
+
+SORT_STATIC_MAX_PAIRS = 1 << 20  # RT_SORT_STATIC_MAX_PAIRS (include/rt_core.h)
 
 
 def device_count():

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1372,6 +1373,96 @@ extern "C" int rt_scene_download_bvh(rt_ctx *ctx, void *nodes32, int32_t node_ca
         RT_CUDA(ctx, cudaMemcpyAsync(order, ctx->d_order, (size_t)ctx->ds.tri_count * sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
         RT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
+    return RT_OK;
+}
+
+// ---- rt_sort_pairs_static: the reorder pass for callers that cannot allocate ----------------------------------------------
+// No counterpart in the reference. Same kernels as rt_sort_pairs
+// (sort_histogram_kernel + one sort_scatter_kernel per digit), but every byte of scratch - digit histograms, tile counters,
+// tile status words, the ping-pong (key, value) buffers of the intermediate digit passes - lives in ONE file-scope device
+// array instead of cudaMalloc'ed buffers. Every GPU that loads the library holds the array (9.3 MiB) until the process exits.
+// All calls on a device share it: it keeps the last call's contents (what must start at zero is cleared per call), and two
+// calls that overlap on the GPU (two streams, two host threads, two contexts on one device) race.
+namespace {
+constexpr int kStaticSortMaxPairs = 1 << 20;  // RT_SORT_STATIC_MAX_PAIRS in rt_core.h
+constexpr size_t kStaticSortHeadWords = (size_t)kSortMaxPasses * 256 + 16;  // histograms + tile counters (word 8 of them: the pair count)
+constexpr size_t kStaticSortMaxTiles = ((size_t)kStaticSortMaxPairs + kSortTile - 1) / kSortTile;  // for the smallest tile
+constexpr size_t kStaticSortStatusWords = (size_t)kSortMaxPasses * kStaticSortMaxTiles * 256;
+constexpr size_t kStaticSortWords = kStaticSortHeadWords + kStaticSortStatusWords + 2 * (size_t)kStaticSortMaxPairs;
+static_assert(RT_SORT_STATIC_MAX_PAIRS == kStaticSortMaxPairs, "rt_core.h and rt_core.cu disagree on the limit");
+}  // namespace
+
+// In HOST code this name is a stand-in for the symbol, not a device address: the address comes from cudaGetSymbolAddress.
+static __device__ __align__(256) uint32_t g_static_sort_scratch[kStaticSortWords];
+
+namespace {
+__global__ void static_sort_set_count_kernel(uint32_t *count, uint32_t n) { *count = n; }
+
+// Device address of the array on `device` (which must be current): looked up once per device, then cached.
+int static_sort_scratch_address(rt_ctx *ctx, int device, uint32_t **out)
+{
+    constexpr int kMaxDevices = 64;
+    static uint32_t *cached[kMaxDevices] = {};
+    static std::mutex lock;
+    if (device < 0 || device >= kMaxDevices) return fail(ctx, RT_ERR_INVALID, "rt_sort_pairs_static: device index beyond 63");
+    std::lock_guard<std::mutex> guard(lock);
+    if (!cached[device]) {
+        void *ptr = nullptr;
+        RT_CUDA(ctx, cudaGetSymbolAddress(&ptr, g_static_sort_scratch));
+        if (!ptr) return fail(ctx, RT_ERR_CUDA, "rt_sort_pairs_static: cudaGetSymbolAddress returned a null address");
+        cached[device] = static_cast<uint32_t *>(ptr);
+    }
+    *out = cached[device];
+    return RT_OK;
+}
+}  // namespace
+
+extern "C" int rt_sort_pairs_static(rt_ctx *ctx, const uint32_t *d_keys_in, const uint32_t *d_values_in, uint32_t *d_keys_out,
+                                    uint32_t *d_values_out, int32_t n, int32_t bits)
+{
+    if (!ctx || n < 0 || bits <= 0 || bits > 32) return fail(ctx, RT_ERR_INVALID, "rt_sort_pairs_static: bad argument");
+    if (n == 0) return RT_OK;  // an empty batch needs no buffers
+    if (!d_keys_in || !d_values_in || !d_keys_out || !d_values_out) return fail(ctx, RT_ERR_INVALID, "rt_sort_pairs_static: null device pointer");
+    if (n > kStaticSortMaxPairs)
+        return fail(ctx, RT_ERR_INVALID, "rt_sort_pairs_static: n = " + std::to_string(n) + " pairs exceeds the static scratch (RT_SORT_STATIC_MAX_PAIRS = " +
+                                             std::to_string(kStaticSortMaxPairs) + "); use rt_sort_pairs, which allocates");
+    if (d_keys_in == d_keys_out || d_values_in == d_values_out) return fail(ctx, RT_ERR_INVALID, "rt_sort_pairs_static: inputs and outputs must not alias");
+    RT_CUDA(ctx, cudaSetDevice(ctx->device));
+    uint32_t *scratch = nullptr;
+    int rc = static_sort_scratch_address(ctx, ctx->device, &scratch);
+    if (rc != RT_OK) return rc;
+
+    const int passes = std::min(kSortMaxPasses, std::max(1, (bits + 7) / 8));
+    const int items = 22, tile_keys = kSortBlock * items;  // the digit pass of the default configuration (ballot ranking)
+    const uint32_t tiles = (uint32_t)(((size_t)n + tile_keys - 1) / tile_keys);
+    SortArgs s;
+    s.hist = scratch;
+    s.tile_counter = scratch + kSortMaxPasses * 256;
+    s.count_ptr = s.tile_counter + 8;
+    s.tile_status = scratch + kStaticSortHeadWords;
+    s.passes = passes;
+    s.max_tiles = tiles;  // stride of the per-pass status arrays
+    uint32_t *tmp_keys = scratch + kStaticSortHeadWords + kStaticSortStatusWords, *tmp_vals = tmp_keys + kStaticSortMaxPairs;
+    cudaStream_t stream = ctx->stream;
+    // the array holds the previous call's histograms, counters and status flags: clear them (the ping-pong part is overwritten
+    // before it is read)
+    RT_CUDA(ctx, cudaMemsetAsync(scratch, 0, (kStaticSortHeadWords + (size_t)passes * tiles * 256) * sizeof(uint32_t), stream));
+    static_sort_set_count_kernel<<<1, 1, 0, stream>>>(const_cast<uint32_t *>(s.count_ptr), (uint32_t)n);
+    const int hist_blocks = (int)std::min<size_t>((size_t)ctx->sm_count * 8, std::max<size_t>(1, ((size_t)n + kSortBlock - 1) / kSortBlock));
+    sort_histogram_kernel<<<hist_blocks, kSortBlock, 0, stream>>>(d_keys_in, s);
+    constexpr int kStage = kSortBlock * 22 * 8;
+    RT_CUDA(ctx, cudaFuncSetAttribute(sort_scatter_kernel<2, 22>, cudaFuncAttributeMaxDynamicSharedMemorySize, kStage));
+    // in -> ... -> out through the one temporary pair: the LAST pass must land in the caller's output
+    const uint32_t *src_k = d_keys_in, *src_v = d_values_in;
+    for (int p = 0; p < passes; p++) {
+        const bool to_out = ((passes - 1 - p) & 1) == 0;
+        uint32_t *dst_k = to_out ? d_keys_out : tmp_keys, *dst_v = to_out ? d_values_out : tmp_vals;
+        sort_scatter_kernel<2, 22><<<tiles, kSortBlock, kStage, stream>>>(src_k, src_v, dst_k, dst_v, s, p);
+        src_k = dst_k;
+        src_v = dst_v;
+    }
+    RT_CUDA(ctx, cudaGetLastError());
+    RT_CUDA(ctx, cudaStreamSynchronize(stream));
     return RT_OK;
 }
 

@@ -212,6 +212,17 @@ int rt_process_rays(rt_ctx *ctx, float *ray_data12, const uint32_t *seeds, int32
 int rt_sort_pairs(rt_ctx *ctx, uint32_t *keys, uint32_t *values, int32_t n, int32_t bits);
 /* CUDA-event time of the sort kernels of the last rt_sort_pairs call (copies excluded), in milliseconds. */
 double rt_sort_device_ms(const rt_ctx *ctx);
+/* The same stable sort for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc). NO COUNTERPART IN THE REFERENCE. DEVICE pointers in and out
+ * (keys / values of n pairs each; inputs are not modified and must not alias the outputs); the call makes no cudaMalloc,
+ * cudaFree or other allocating call. All scratch (digit histograms, tile status, the buffers of the intermediate digit
+ * passes) is one static device array of the library: 9.3 MiB that every GPU which loads the library holds until the process
+ * exits, sized for n <= RT_SORT_STATIC_MAX_PAIRS; a larger n is rejected with RT_ERR_INVALID and a message. Every call on a
+ * device shares that array: calls that overlap on the GPU (two host threads, two contexts on one device) race, so serialise
+ * them. Runs on the context's stream and returns after it has drained. */
+#define RT_SORT_STATIC_MAX_PAIRS (1 << 20)
+int rt_sort_pairs_static(rt_ctx *ctx, const uint32_t *d_keys_in, const uint32_t *d_values_in, uint32_t *d_keys_out,
+                         uint32_t *d_values_out, int32_t n, int32_t bits);
 /* Measurement aid: device-to-device copy of `bytes` (read + write counted) repeated `iters` times after a warm-up, GB/s by
  * CUDA events. With a buffer pair that fits the L2 it gives the L2 bandwidth bench.py's roofline.l2_frac is quoted against;
  * with a large one, the HBM copy bandwidth (the figure MEASURED_PEAKS.json holds). */
