@@ -228,7 +228,8 @@ def ref_gpu_timing(scene, w, h, bounces, lpp):
     depend on the sample count; the steady-state rate is therefore the least-squares SLOPE of `GPU Took` over five sample
     counts (whole passes of 20), every point the best of three runs after one discarded warm-up run per mode. Reported with
     the standard error of the slope (`spread`) and the largest residual, so that a noisy box shows."""
-    pts = (100, 200, 300, 400, 500) if w * h <= 1_000_000 else (20, 40, 60, 80, 100)
+    # sample counts far enough apart that the slope stands clear of the timer's ~20 ms run-to-run jitter (spheres at 1000x1000: 0.2 ms per spp)
+    pts = (200, 600, 1000, 1400, 1800) if w * h <= 1_000_000 else (20, 40, 60, 80, 100)
     paths = {spp: _scene_file_with_image(scene, w, h, spp, bounces) for spp in pts}
 
     def took(spp, flags):
@@ -277,8 +278,9 @@ def newest_ncu_summary(build=None):
             continue
         d["_file"] = os.path.relpath(f, ROOT)
         found.append(d)
-    same = [d for d in found if d.get("build_id") == build and "nodes=f32" in d.get("workload", "")]
-    return (same or found or [None])[-1]
+    f32 = [d for d in found if "nodes=f32" in d.get("workload", "")]  # the default node format's captures
+    same = [d for d in f32 if d.get("build_id") == build]
+    return (same or f32 or found or [None])[-1]
 
 
 def main():
