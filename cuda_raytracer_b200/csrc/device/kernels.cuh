@@ -21,10 +21,13 @@ namespace rtd {
 
 constexpr int kBlock = kTraceBlock;  // threads per CTA of the traversal kernels (128)
 constexpr int kBlocksPerSM = 6;       // process_kernel (parity hook): full-depth stack in shared memory, 6 x 32 KB
+// RT_TRACE_CTAS: minimum CTAs per SM given to the tracer's __launch_bounds__, i.e. its register cap. 10 -> 48 registers, no
+// spills, 40 warps per SM. Measured (profiles/r2d_tracer_occupancy.log, lamp 4K / teapot / cornell_plus, two runs each):
+// 8 (55 regs) +0.5 / +0.7 / +1.2 %, 10 +1.4 / +1.2 / +1.3 %, 12 (40 regs, 8-24 B spilled) +0.9 / +0.5 / +1.7 % against round 1's 9.
 #ifndef RT_TRACE_CTAS
-#define RT_TRACE_CTAS 9
+#define RT_TRACE_CTAS 10
 #endif
-constexpr int kBlocksPerSMLocal = RT_TRACE_CTAS;  // tracer: 8 CTAs -> 32 warps per SM, <= 64 registers per thread
+constexpr int kBlocksPerSMLocal = RT_TRACE_CTAS;
 
 __device__ __forceinline__ uint32_t lanemask_lt() { return (1u << (threadIdx.x & 31)) - 1u; }
 
