@@ -114,6 +114,8 @@ constexpr int kMaxBounces = 256;  // the reference has no limit; these per-bounc
 struct PassCounters {
     uint32_t cursor[kMaxBounces + 1];  // work-fetch cursor of bounce b
     uint32_t count[kMaxBounces + 1];   // live rays entering bounce b (count[0] unused: known on the host)
+    uint32_t tail_bounce;              // 0 = the bounce-by-bounce launches are still running this wave; b >= 2 = tail_kernel took
+                                       // over at bounce b (every later trace / shade / tail launch of the wave returns at once)
 };
 
 struct RenderTotals {
@@ -133,6 +135,7 @@ struct BounceArgs {
     float *framebuffer;     // 3 floats per pixel, un-normalised sums
     uint32_t n_first;       // rays of the wave = group x pass_rays (bounce 0 only)
     uint32_t pass_rays;     // rays of ONE pass (pixels x rays_per_pixel); ray id = pass-in-wave x pass_rays + index in pass
+    uint32_t partial_g;     // member of the wave that is a PARTIAL pass (always the last one; 0xFFFFFFFF = none): the three fields below are its
     uint32_t ray_offset;    // a wave that holds PART of one pass (rt_render_opts.ray_first / ray_count): index in pass = id + ray_offset
     uint32_t sub_count;     // > 0: the wave holds samples [sub_first, sub_first + sub_count) of EVERY pixel of one pass
     uint32_t sub_first;     //      (rt_render_opts.sample_first / sample_count): index in pass = (id / sub_count) * rays_per_pixel + sub_first + id % sub_count
@@ -147,6 +150,8 @@ struct BounceArgs {
     uint32_t trace_batch, trace_refill_below, trace_node_min;  // TraceTuning
     const uint4 *entry_lists;  // per-tile entry records for primary rays (entry_lists.cuh), nullptr = start at the root
     int32_t entry_tiles_x;
+    int32_t bounces_total;  // the frame's bounce limit (tail_kernel runs a ray from a.bounce to its end)
+    uint32_t tail_below;    // tail_kernel takes the wave over when at most this many rays enter its bounce (0 = never)
 };
 
 }  // namespace rtd

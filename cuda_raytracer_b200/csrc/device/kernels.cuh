@@ -33,8 +33,9 @@ __device__ __forceinline__ uint32_t lanemask_lt() { return (1u << (threadIdx.x &
 
 // Ray index INSIDE ITS PASS (what the reference's seeds and pixel are functions of: raytracing.cu:89, scene.cu:81,83) of the
 // ray with number j inside the wave's pass: j itself for whole passes, shifted for a ray range, strided for a sample range.
-__device__ __forceinline__ uint32_t pass_index(const BounceArgs &a, uint32_t j)
+__device__ __forceinline__ uint32_t pass_index(const BounceArgs &a, uint32_t j, uint32_t g)
 {
+    if (g != a.partial_g) return j;  // a whole pass
     if (a.sub_count == 0u) return j + a.ray_offset;
     const uint32_t px = fast_div(j, a.div_sub_count);
     return px * (uint32_t)a.rays_per_pixel + a.sub_first + (j - px * a.sub_count);
@@ -68,6 +69,13 @@ __device__ __forceinline__ void add_radiance(float *framebuffer, uint32_t pixel,
     if (c.z != 0.0f) atomicAdd(framebuffer + 3 * (size_t)pixel + 2, c.z);
 }
 
+// True once tail_kernel has taken this wave over at an earlier (or this) bounce: the bounce's own launches have nothing to do.
+__device__ __forceinline__ bool tail_took_over(const BounceArgs &a)
+{
+    const uint32_t tb = *reinterpret_cast<volatile const uint32_t *>(&a.pc->tail_bounce);
+    return tb != 0u && tb <= (uint32_t)a.bounce;
+}
+
 // ---- the wavefront pair of one bounce ------------------------------------------------------------------------------
 // trace_rays_kernel: closest hit of every ray of the bounce's queue -> hit record {t, prim} per queue position.
 // Persistent warps, per-lane refill (traverse.cuh). Bounce 0 generates its rays from the ray id instead of reading
@@ -80,7 +88,7 @@ struct QueueTraceIO {
     {
         if (FIRST) {
             const uint32_t g = fast_div(i, a.div_pass_rays);  // pass of the wave; seeds and pixel follow the index inside that pass
-            if (!generate_ray(sc, pass_index(a, i - g * a.pass_rays), a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d)) return false;
+            if (!generate_ray(sc, pass_index(a, i - g * a.pass_rays, g), a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d)) return false;
         } else {
             const uint32_t slot = a.order ? __ldg(a.order + i) : i;
             const float4 ra = __ldcs(a.in.qa + slot), rb = __ldcs(a.in.qb + slot);
@@ -103,7 +111,7 @@ struct QueueTraceIO {
         cur = 0;
         if (!FIRST || !use_entries) return;
         const uint32_t g = fast_div(i, a.div_pass_rays);
-        const uint32_t pixel = fast_div(pass_index(a, i - g * a.pass_rays), a.div_rays_per_pixel);
+        const uint32_t pixel = fast_div(pass_index(a, i - g * a.pass_rays, g), a.div_rays_per_pixel);
         const uint32_t y = fast_div(pixel, sc.div_width), x = pixel - y * (uint32_t)sc.width;
         const uint4 *rec = a.entry_lists + 4 * (size_t)((y / kEntryTile) * (uint32_t)a.entry_tiles_x + x / kEntryTile);
         const uint4 q0 = __ldg(rec), q1 = __ldg(rec + 1), q2 = __ldg(rec + 2), q3 = __ldg(rec + 3);
@@ -145,6 +153,7 @@ struct StackSlots {
 template <bool FIRST, bool STATS, int NODES>
 __global__ void __launch_bounds__(kBlock, kBlocksPerSMLocal) trace_rays_kernel(const DeviceScene sc, const BounceArgs a)
 {
+    if (!FIRST && tail_took_over(a)) return;
     const uint32_t n_in = FIRST ? a.n_first : a.pc->count[a.bounce];
     TraceCounters ctr;
     // the counting variant walks from the root; the entry records are cut from the binary tree's numbering
@@ -173,6 +182,7 @@ constexpr int kShadeBlock = RT_SHADE_BLOCK;  // multiple of 128 (the octant scan
 template <bool FIRST>
 __global__ void RT_SHADE_BOUNDS shade_kernel(const DeviceScene sc, const BounceArgs a)
 {
+    if (!FIRST && tail_took_over(a)) return;
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t n_in = FIRST ? a.n_first : a.pc->count[a.bounce];
     uint32_t *out_count = &a.pc->count[a.bounce + 1];
@@ -221,7 +231,7 @@ __global__ void RT_SHADE_BOUNDS shade_kernel(const DeviceScene sc, const BounceA
         if (active) {
             if (FIRST) {
                 const uint32_t g = fast_div(id, a.div_pass_rays);
-                active = generate_ray(sc, pass_index(a, id - g * a.pass_rays), a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d);
+                active = generate_ray(sc, pass_index(a, id - g * a.pass_rays, g), a.div_rays_per_pixel, a.gen_seed[g], a.pcg_inc, o, d);
             } else {
                 o = f3(cur.ra.x, cur.ra.y, cur.ra.z);
                 d = f3(cur.ra.w, cur.rb.x, cur.rb.y);
@@ -236,7 +246,7 @@ __global__ void RT_SHADE_BOUNDS shade_kernel(const DeviceScene sc, const BounceA
             const float2 h = cur.h;
             const float closest = h.x;
             const int prim = __float_as_int(h.y);
-            const uint32_t g = fast_div(id, a.div_pass_rays), index = pass_index(a, id - g * a.pass_rays);  // pass of the wave, ray index inside it
+            const uint32_t g = fast_div(id, a.div_pass_rays), index = pass_index(a, id - g * a.pass_rays, g);  // pass of the wave, ray index inside it
             pixel = fast_div(index, a.div_rays_per_pixel);
             if (prim < 0) {
                 radiance = shade_miss(sc, d) * T;
@@ -285,6 +295,63 @@ __global__ void RT_SHADE_BOUNDS shade_kernel(const DeviceScene sc, const BounceA
             }
             // no barrier here: the next iteration writes the other buffer, and this one is rewritten only after every
             // thread has passed that iteration's first barrier
+        }
+    }
+}
+
+// ---- tail_kernel: the stragglers of a wave, run to completion in ONE launch -------------------------------------------
+// From bounce ~4 on a wave holds 0.1-3 % of its rays, and every bounce is still a trace + a shade launch whose duration is the
+// latency of its LONGEST ray (teapot: 6 x ~0.35 ms per wave for rays that make up 0.3 % of the work; that fixed cost per wave is
+// what limits strong scaling of small frames, profiles/r2f_tail.md). Launched in front of every bounce b >= 2, this kernel does
+// nothing until at most a.tail_below rays enter its bounce; then each thread takes rays of that queue and runs them through
+// ALL their remaining bounces (closest hit + shading per bounce, the same device functions and the same per-(ray, bounce)
+// seeds as the wavefront launches: proc_seed of bounce b' = proc_seed of bounce b + 279220567 (b' - b), raytracing.cu:89,236),
+// and marks the wave so that the later launches of the wave return at once. Same hits, same radiance up to the order of the
+// float atomics, same live-ray counters.
+constexpr int kTailCtasPerSM = 6;  // 32 KB of shared-memory stack per CTA
+__global__ void __launch_bounds__(kBlock, kTailCtasPerSM) tail_kernel(const DeviceScene sc, const BounceArgs a)
+{
+    const uint32_t tb = *reinterpret_cast<volatile const uint32_t *>(&a.pc->tail_bounce);
+    if (tb != 0u && tb < (uint32_t)a.bounce) return;  // taken over at an earlier bounce (tb == a.bounce: by a CTA of this launch)
+    const uint32_t n_in = a.pc->count[a.bounce];
+    if (n_in > a.tail_below) return;
+    if (blockIdx.x == 0 && threadIdx.x == 0) a.pc->tail_bounce = (uint32_t)a.bounce;  // also when n_in == 0: the wave is over
+
+    __shared__ SharedStack<kBlock> stack;
+    __shared__ uint32_t live_sh[kMaxBounces];
+    for (int b = threadIdx.x; b < kMaxBounces; b += kBlock) live_sh[b] = 0u;
+    __syncthreads();
+    TraceCounters ctr;
+    for (uint32_t i = blockIdx.x * kBlock + threadIdx.x; i < n_in; i += gridDim.x * kBlock) {
+        const float4 ra = __ldcs(a.in.qa + i), rb = __ldcs(a.in.qb + i);
+        const float2 rc = __ldcs(a.in.qc + i);
+        float3 o = f3(ra.x, ra.y, ra.z), d = f3(ra.w, rb.x, rb.y), T = f3(rb.z, rb.w, rc.x);
+        const uint32_t id = __float_as_uint(rc.y);
+        const uint32_t g = fast_div(id, a.div_pass_rays), index = pass_index(a, id - g * a.pass_rays, g);
+        const uint32_t pixel = fast_div(index, a.div_rays_per_pixel);
+        for (int b = a.bounce; b < a.bounces_total; b++) {
+            atomicAdd(&live_sh[b], 1u);
+            float closest = kMissT;
+            int prim = -1;
+            intersect_spheres(sc, o, d, closest, prim);
+            traverse_bvh<kBlock, false>(sc, o, d, closest, prim, stack, ctr);
+            if (prim < 0) {
+                add_radiance(a.framebuffer, pixel, shade_miss(sc, d) * T);
+                break;
+            }
+            Pcg rng = pcg_seed(index * 4137874753u + a.proc_seed[g] + 279220567u * (uint32_t)(b - a.bounce), a.pcg_inc);
+            float3 emitted;
+            shade_hit(sc, o, d, closest, prim, T, rng, emitted);
+            add_radiance(a.framebuffer, pixel, emitted);
+            if (is_zero(T)) break;
+        }
+    }
+    __syncthreads();
+    for (int b = threadIdx.x; b < kMaxBounces; b += kBlock) {
+        const uint32_t v = live_sh[b];
+        if (v) {
+            atomicAdd(&a.totals->live_ray_bounces, (unsigned long long)v);
+            atomicAdd(&a.totals->live_per_bounce[min(b, 31)], (unsigned long long)v);
         }
     }
 }

@@ -75,6 +75,7 @@ struct rt_ctx {
     uint32_t trace_batch = kBatch, trace_refill_below = kRefillBelow, trace_node_min = kNodeMin;  // RT_BATCH / RT_REFILL override
     uint32_t *d_keys[2] = {nullptr, nullptr}, *d_vals[2] = {nullptr, nullptr};
     size_t sort_capacity = 0;
+    uint32_t tail_below = 0;   // RT_TAIL: tail_kernel takes a wave over when at most this many rays enter a bounce (0 = off)
     int sort_rank = 2, sort_items = kSortItems;  // RT_SORT_RANK / RT_SORT_ITEMS: ranking variant and keys per thread of the digit pass
     uint32_t *d_sort_scratch = nullptr;  // hist + tile counters + tile status
     size_t sort_scratch_words = 0;
@@ -336,6 +337,7 @@ static int init_context(rt_ctx *ctx, int device)
     if (const char *e = std::getenv("RT_NODES")) ctx->node_mode = std::strcmp(e, "q16") == 0 ? kNodesQ16 : std::strcmp(e, "w4") == 0 ? kNodesW4 : kNodesF32;
     if (const char *e = std::getenv("RT_SORT_RANK")) ctx->sort_rank = std::min(2, std::max(0, std::atoi(e)));
     if (const char *e = std::getenv("RT_SORT_ITEMS")) { const int v = std::atoi(e); ctx->sort_items = v <= 12 ? 12 : v <= 16 ? 16 : v <= 18 ? 18 : v <= 22 ? 22 : 26; }
+    if (const char *e = std::getenv("RT_TAIL")) ctx->tail_below = (uint32_t)std::max(0L, std::atol(e));
     if (const char *e = std::getenv("RT_ENTRY_K")) ctx->entry_max = std::min((int)kEntryMax, std::max(0, std::atoi(e)));
     if (const char *e = std::getenv("RT_BATCH")) ctx->trace_batch = (uint32_t)std::min(4096, std::max(4, std::atoi(e)));
     if (const char *e = std::getenv("RT_NODEMIN")) ctx->trace_node_min = (uint32_t)std::min(33, std::max(0, std::atoi(e)));
@@ -930,6 +932,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         const size_t per_pass = pass_rays_max * (size_t)(88 + (sort ? 16 : 0));    // 2 x 40 B queues + 8 B hit (+ keys, permutation)
         max_group = (int)std::max<size_t>(1, (free_b + have) / 10 * 7 / std::max<size_t>(1, per_pass));
     }
+    const int mem_group = std::max(1, max_group);  // passes whose queues fit in memory (over all pipes), before any other limit
     max_group = std::max(1, std::min({max_group, (int)kMaxPassGroup, std::max(1, n_segs)}));
     // ray ids are 31-bit; the reorder pass keeps tile counts in 30 bits next to its two status flags (radix_sort.cuh)
     const size_t wave_limit = sort ? (1ull << 30) : (1ull << 31);
@@ -943,7 +946,9 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     // scratch is single), not with per-kernel event timing or counting (their numbers are per kernel, alone on the GPU).
     int pipes = (sort || timing || collect || opts.single_pipe || n_segs < 2) ? 1 : ctx->pipes;
     pipes = std::max(1, std::min(pipes, n_segs));
-    if (pipes > 1 && opts.pass_group <= 0) max_group = std::max(1, std::min(max_group / pipes, (n_segs + pipes - 1) / pipes));
+    // automatic wave size with several pipes: the work split evenly over the pipes (rounded UP: 5 passes on 2 pipes are waves of
+    // 3 + 2, not 2 + 2 + 1 — every wave pays a fixed chain of latency-bound late bounces), within each pipe's share of the memory
+    if (pipes > 1 && opts.pass_group <= 0) max_group = std::max(1, std::min({max_group, mem_group / pipes, (n_segs + pipes - 1) / pipes}));
     // the automatic wave size is a guess at what the allocator will grant: on an out-of-memory answer try smaller waves
     for (;;) {
         rc = ensure_queues(ctx, pass_rays_max * (size_t)max_group * (size_t)pipes, sort);
@@ -963,6 +968,9 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     // entry records of the primary rays: cut once per scene + camera, reused by every pass and frame
     const int tiles_x = (ctx->ds.width + kEntryTile - 1) / kEntryTile, tiles_y = (ctx->ds.height + kEntryTile - 1) / kEntryTile;
     const bool use_entries = ctx->entry_max > 0 && opts.root_start == 0;
+    // tail_kernel (kernels.cuh) walks the float records from the queue in its own order: not with the reorder pass (permuted
+    // queue), the counting variant (it does not count visits) or the compressed node formats
+    const bool use_tail = ctx->tail_below > 0 && !sort && !collect && ctx->active_nodes == kNodesF32;
     if (use_entries && ctx->entry_dirty) {
         if ((rc = reserve(ctx, &ctx->d_entry, &ctx->cap_entry, (size_t)tiles_x * tiles_y * 64)) != RT_OK) return rc;
         build_entry_lists_kernel<<<(tiles_x * tiles_y + 127) / 128, 128, 0, ctx->stream>>>(ctx->ds, tiles_x, tiles_y, ctx->entry_max, (uint4 *)ctx->d_entry);
@@ -994,17 +1002,35 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     // A WAVE is `group` consecutive passes of equal size traced together: every pass keeps the reference's seeds
     // (they depend on the pass, not on the launch), while the late bounces - a few 10^4 rays per pass, latency-bound -
     // and the launch gaps are paid once per wave instead of once per pass.
-    for (int si = 0; si < n_segs;) {
-        const int pass = segs[si].pass;
-        const int rays_to_cast = spp_of(pass);
-        const bool partial = !whole(segs[si]);
-        const uint32_t pass_rays = partial ? segs[si].count : (uint32_t)(pixels * (size_t)rays_to_cast);
-        int group = 1;  // a partial pass is a wave of its own
-        while (!partial && group < max_group && si + group < n_segs && whole(segs[si + group]) && spp_of(segs[si + group].pass) == rays_to_cast)
-            group++;
+    // Whole passes first, partial passes (the ends of a ray / sample range) after them: a partial pass rides along as the LAST
+    // member of a wave of whole passes with the same samples per pixel (the member index of a ray is id / pass_rays, which needs
+    // full-size members in front). On its own it would be a whole chain of latency-bound launches for a fraction of a pass: a
+    // quarter pass as its own wave cost teapot's 8-GPU share 2 ms of 19 (profiles/r2f_partial.md).
+    std::stable_partition(segs.begin(), segs.end(), whole);
+    const int n_whole = (int)(std::find_if(segs.begin(), segs.end(), [&](const Segment &g) { return !whole(g); }) - segs.begin());
+    int wi = 0, pi = n_whole;  // next whole pass, next partial pass
+    while (wi < n_whole || pi < n_segs) {
+        Segment member[kMaxPassGroup];
+        int group = 0, partial_member = -1;
+        if (wi < n_whole) {
+            const int spp0 = spp_of(segs[wi].pass);
+            const int room = std::max(1, max_group - (pi < n_segs ? 1 : 0));  // keep a slot for a partial pass that is waiting
+            while (group < room && wi < n_whole && spp_of(segs[wi].pass) == spp0) member[group++] = segs[wi++];
+            if (pi < n_segs && group < max_group && spp_of(segs[pi].pass) == spp0 && (size_t)segs[pi].count < pixels * (size_t)spp0) {
+                partial_member = group;
+                member[group++] = segs[pi++];
+            }
+        } else {  // only partial passes are left: each is a wave of its own
+            partial_member = 0;
+            member[group++] = segs[pi++];
+        }
+        const int rays_to_cast = spp_of(member[0].pass);
+        const bool partial = partial_member >= 0;
+        const Segment &pseg = member[partial ? partial_member : 0];
+        const uint32_t pass_rays = partial_member == 0 ? pseg.count : (uint32_t)(pixels * (size_t)rays_to_cast);
         int remaining[kMaxPassGroup];  // the reference's `remaining_rays` after the decrement (:224-225), per pass
-        for (int g = 0; g < group; g++) remaining[g] = ctx->ray_count - segs[si + g].pass * pass_spp - rays_to_cast;
-        const uint32_t total = pass_rays * (uint32_t)group;
+        for (int g = 0; g < group; g++) remaining[g] = ctx->ray_count - member[g].pass * pass_spp - rays_to_cast;
+        const uint32_t total = partial_member > 0 ? pass_rays * (uint32_t)(group - 1) + pseg.count : pass_rays * (uint32_t)group;
         primaries += total;
         const int pipe = wave++ % pipes;
         cur_stream = pipe ? ctx->side[pipe - 1] : ctx->stream;
@@ -1025,9 +1051,10 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             a.framebuffer = ctx->d_fb;
             a.n_first = total;
             a.pass_rays = pass_rays;
-            a.ray_offset = partial ? segs[si].offset : 0u;
-            a.sub_count = partial ? segs[si].sub_count : 0u;
-            a.sub_first = partial ? segs[si].sub_first : 0u;
+            a.partial_g = partial ? (uint32_t)partial_member : 0xFFFFFFFFu;
+            a.ray_offset = partial ? pseg.offset : 0u;
+            a.sub_count = partial ? pseg.sub_count : 0u;
+            a.sub_first = partial ? pseg.sub_first : 0u;
             a.div_sub_count = make_fast_div(std::max(1u, a.sub_count));
             a.bounce = b;
             a.rays_per_pixel = rays_to_cast;
@@ -1045,9 +1072,18 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             a.trace_node_min = ctx->trace_node_min;
             a.entry_lists = use_entries ? (const uint4 *)ctx->d_entry : nullptr;
             a.entry_tiles_x = tiles_x;
+            a.bounces_total = ctx->bounces;
+            a.tail_below = use_tail ? ctx->tail_below : 0u;
             // the live count of bounce b > 0 exists only on the device: size the grids for the pass's upper bound
             const int shade_grid = (int)std::min<size_t>((size_t)shade_grid_max, ((size_t)total + kShadeBlock - 1) / kShadeBlock);
             const int t_grid = (int)std::min<size_t>((size_t)grid, ((size_t)total + kBlock - 1) / kBlock);
+            if (use_tail && b >= 2) {  // the wave's stragglers in one launch (a no-op until few enough rays are left)
+                const int tail_grid = (int)std::min<size_t>((size_t)ctx->sm_count * kTailCtasPerSM, ((size_t)std::min<uint32_t>(ctx->tail_below, total) + kBlock - 1) / kBlock);
+                if ((rc = mark(0)) != RT_OK) return fail(ctx, rc, "event record failed");
+                tail_kernel<<<std::max(1, tail_grid), kBlock, 0, cur_stream>>>(ctx->ds, a);
+                if ((rc = mark(0)) != RT_OK) return fail(ctx, rc, "event record failed");
+                launches++;
+            }
             if ((rc = mark(0)) != RT_OK) return fail(ctx, rc, "event record failed");
             if (b == 0) launch_trace<true>(ctx, cur_stream, collect, t_grid, a);
             else launch_trace<false>(ctx, cur_stream, collect, t_grid, a);
@@ -1067,7 +1103,6 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             }
         }
         passes_done += group;
-        si += group;
     }
     if (pipes > 1) {
         for (int i = 0; i < pipes - 1; i++) {
