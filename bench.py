@@ -434,7 +434,14 @@ def main():
                            "ok": bool(rel_rmse <= 1e-4 and int(live_first.item()) == int(r.last_stats.live_ray_bounces))}
         dist.barrier()
 
+    per_rank_ms = None
     if dist is not None:
+        # every rank's own pass loop and reduce interval (ms per step): the reduce interval of a rank that finishes its
+        # share early is mostly the wait for the slowest rank, so the spread of the loops is the number to read
+        mine = torch.tensor([(dev_s - red_s) / args.steps * 1e3, red_s / args.steps * 1e3], dtype=torch.float64, device="cuda")
+        every = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine)
+        per_rank_ms = {"pass_loop": [round(float(v[0]), 3) for v in every], "reduce_interval": [round(float(v[1]), 3) for v in every]}
         t = torch.tensor([dev_s, e2e_s, tr_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_s, e2e_s, tr_ms_max = (float(v) for v in t)
@@ -515,6 +522,8 @@ def main():
     }
     if image_check is not None:
         line["multi_gpu_image_check"] = image_check
+    if per_rank_ms is not None:
+        line["per_rank_ms_per_step"] = per_rank_ms
     extras = world == 1 and not args.no_extras
     if extras:  # the same tree built on the device (csrc/device/bvh_build.cuh) vs the host builder
         dev_scene = rt.load_scene(scene_name + ".scene", use_bvh="device", cwd=SCENES).set_image(w, h, spp, bounces)

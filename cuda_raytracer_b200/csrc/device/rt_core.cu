@@ -32,7 +32,7 @@ struct rt_ctx {
     static constexpr int kMaxPipes = 4;
     cudaStream_t side[kMaxPipes - 1] = {};  // further pipes of the pass loop: wave w runs on pipe w % pipes (render_impl)
     cudaEvent_t ev_fork = nullptr, ev_join[kMaxPipes - 1] = {};
-    int pipes = 2;                   // RT_PIPES=1: one wave at a time
+    int pipes = 0;                   // 0 = automatic (render_impl); RT_PIPES=1: one wave at a time, 2..4: that many
     int trace_per_sm = 0;            // RT_TRACE_PER_SM: CTAs per SM of the persistent tracer grid (0 = full occupancy)
     int shade_per_sm = 0;            // RT_SHADE_PER_SM: CTAs per SM of the shade grid (0 = 2048 threads' worth)
     std::string error;
@@ -944,7 +944,12 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     // its CTAs instead of idling, and the HBM-latency-bound shade kernel of one wave overlaps the issue-bound tracer of the
     // other. The automatic wave size is divided by the pipes so that the memory in use stays the same. Not with the reorder pass (its
     // scratch is single), not with per-kernel event timing or counting (their numbers are per kernel, alone on the GPU).
-    int pipes = (sort || timing || collect || opts.single_pipe || n_segs < 2) ? 1 : ctx->pipes;
+    // Automatic: 2; 3 for a call of at most 8 passes (one GPU's share of a small frame). Such a call is two or three waves in all, the
+    // fixed chain of late bounces is a tenth of it, and three smaller waves leave less of that chain without company than two
+    // (teapot 1000x1000, samples [0, 125): 17.67 ms on 2 pipes, 17.11 on 3, 17.25 on 4; profiles/r2f_partial.md). Whole frames
+    // measured no gain from a third pipe (profiles/r1k_box_ch.md).
+    const int want_pipes = ctx->pipes > 0 ? ctx->pipes : (n_segs <= 8 ? 3 : 2);
+    int pipes = (sort || timing || collect || opts.single_pipe || n_segs < 2) ? 1 : want_pipes;
     pipes = std::max(1, std::min(pipes, n_segs));
     // automatic wave size with several pipes: the work split evenly over the pipes (rounded UP: 5 passes on 2 pipes are waves of
     // 3 + 2, not 2 + 2 + 1 — every wave pays a fixed chain of latency-bound late bounces), within each pipe's share of the memory

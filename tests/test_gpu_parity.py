@@ -403,6 +403,21 @@ def test_sample_ranges_sum_to_the_whole_frame(renderer):
     assert np.sqrt(np.mean((got - want) ** 2)) / np.sqrt(np.mean(want ** 2)) <= 0.02
     img = renderer.render(sort=False, sample_first=70, sample_count=5)  # past the end: nothing
     assert renderer.last_stats.primary_rays == 0 and not img.any()
+    # shares that hold WHOLE passes and partial ones: the partial pass rides as the last member of a wave of whole passes
+    # (render_impl; BounceArgs.partial_g) — one partial behind one whole pass, two partials around a whole pass (the second of
+    # a shorter pass, which cannot ride), and each with one and with several pipes and wave sizes
+    for kw in ({}, dict(single_pipe=True), dict(pass_group=1), dict(pass_group=2)):
+        acc, live_sum = np.zeros_like(whole, dtype=np.float64), np.zeros(bounces, np.int64)
+        for a, b in ((0, 25), (25, 65), (65, 70)):
+            acc += renderer.render(sort=False, sample_first=a, sample_count=b - a, **kw)
+            live_sum += np.array(renderer.last_stats.live_per_bounce[:bounces], np.int64)
+            assert renderer.last_stats.primary_rays == w * h * (b - a)
+        assert (live_sum == live).all(), kw
+        assert np.allclose(acc, whole, rtol=1e-4, atol=1e-4 * whole.mean()), kw
+    got = renderer.render(sort=False, sample_first=15, sample_count=30)  # partial + whole pass 1 + partial, against the oracle
+    want, ctr = oracle_render_samples(A, 15, 30)
+    assert abs(renderer.last_stats.live_ray_bounces - ctr.live_ray_bounces) <= 2e-3 * ctr.live_ray_bounces
+    assert np.sqrt(np.mean((got - want) ** 2)) / np.sqrt(np.mean(want ** 2)) <= 0.02
 
 
 @pytest.mark.parametrize("shares", [2, 3])

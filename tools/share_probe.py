@@ -1,5 +1,5 @@
 """What one GPU's share of a frame costs against frame / N (the strong-scaling loss that is NOT the collective):
-usage: share_probe.py <scene> <w> <h> <spp> <bounces> <N>  — renders the whole frame, then rank 0's sample share of N, with
+usage: share_probe.py <scene> <w> <h> <spp> <bounces> <N> [ranks]  — renders the whole frame, then rank 0's sample share of N, with
 RT_PIPES / pass_group variants."""
 import json, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -20,7 +20,8 @@ def best(**kw):
     return b
 full = best()
 print(json.dumps({"what": "whole frame", "ms": round(full.loop_seconds * 1e3, 3), "ideal_share_ms": round(full.loop_seconds * 1e3 / N, 3), "launches": full.kernel_launches}))
-for rank in (0, N - 1):
+ranks = [int(v) for v in sys.argv[7].split(",")] if len(sys.argv) > 7 else [0, N - 1]
+for rank in ranks:
     f, c = sample_range(spp, rank, N)
     for label, kw in (("auto", {}), ("single_pipe", dict(single_pipe=True)), ("group1", dict(pass_group=1)), ("group2", dict(pass_group=2)), ("group3", dict(pass_group=3)), ("group8", dict(pass_group=8))):
         s = best(sample_first=f, sample_count=c, **kw)
