@@ -250,15 +250,33 @@ def ref_gpu_timing(scene, w, h, bounces, lpp):
                 out[mode] = {"unavailable": "no `GPU Took` line"}
                 continue
             n = len(pts)
-            mx, my = sum(pts) / n, sum(ys) / n
+            mx = sum(pts) / n
             sxx = sum((x - mx) ** 2 for x in pts)
-            slope = sum((x - mx) * (y - my) for x, y in zip(pts, ys)) / sxx
-            icpt = my - slope * mx
-            res = [y - (icpt + slope * x) for x, y in zip(pts, ys)]
+
+            def fit():
+                my = sum(ys) / n
+                slope = sum((x - mx) * (y - my) for x, y in zip(pts, ys)) / sxx
+                icpt = my - slope * mx
+                return slope, icpt, [y - (icpt + slope * x) for x, y in zip(pts, ys)]
+
+            # The timer's noise is one-sided (an allocation or the upload taking longer): a point that sits ABOVE the line by
+            # more than 3 x the median residual and 2 % of its value is run three more times (best kept), at most twice.
+            remeasured = []
+            for _ in range(2):
+                slope, icpt, res = fit()
+                k = max(range(n), key=lambda j: res[j])
+                med = sorted(abs(r) for r in res)[n // 2]
+                if res[k] <= max(3.0 * med, 0.02 * ys[k]):
+                    break
+                again = [t for t in (took(pts[k], flags) for _ in range(3)) if t]
+                ys[k] = min([ys[k]] + again)
+                remeasured.append(pts[k])
+            slope, icpt, res = fit()
             se = (sum(r * r for r in res) / max(1, n - 2) / sxx) ** 0.5
             rate = lpp * w * h / max(slope, 1e-12) * 1e-6
             out[mode] = {"value": rate, "unit": "Mrays/s", "spread": rate * se / max(slope, 1e-12), "spread_rel": se / max(slope, 1e-12),
-                         "s_per_spp": slope, "fixed_cost_s": icpt, "max_residual_s": max(abs(r) for r in res), "gpu_took_s": dict(zip(pts, ys))}
+                         "s_per_spp": slope, "fixed_cost_s": icpt, "max_residual_s": max(abs(r) for r in res), "gpu_took_s": dict(zip(pts, ys)),
+                         "remeasured_spp": remeasured}
     finally:
         for pth in paths.values():
             os.unlink(pth)
