@@ -222,6 +222,34 @@ def reference_arm(args, rank, world, emit):
 
 
 # ---- the B200 arm ------------------------------------------------------------------------------------------------------
+def slope_fit(xs, ys):
+    """Least-squares line through (xs, ys): slope, intercept, residuals, standard error of the slope."""
+    n = len(xs)
+    mx, my = sum(xs) / n, sum(ys) / n
+    sxx = sum((x - mx) ** 2 for x in xs)
+    slope = sum((x - mx) * (y - my) for x, y in zip(xs, ys)) / sxx
+    icpt = my - slope * mx
+    res = [y - (icpt + slope * x) for x, y in zip(xs, ys)]
+    se = (sum(r * r for r in res) / max(1, n - 2) / sxx) ** 0.5
+    return slope, icpt, res, se
+
+
+def fit_with_remeasure(xs, ys, measure_again, rounds=2):
+    """slope_fit for a timer whose noise is one-sided (an allocation or an upload taking longer, never shorter): a point that sits
+    ABOVE the line by more than 3 x the median absolute residual and 2 % of its value is measured again (`measure_again(x)`
+    returns further samples, the smallest is kept), at most `rounds` times. Modifies ys; returns the fit + the re-measured xs."""
+    remeasured = []
+    for _ in range(rounds):
+        slope, icpt, res, se = slope_fit(xs, ys)
+        k = max(range(len(xs)), key=lambda j: res[j])
+        med = sorted(abs(r) for r in res)[len(xs) // 2]
+        if res[k] <= max(3.0 * med, 0.02 * ys[k]):
+            break
+        ys[k] = min([ys[k]] + list(measure_again(xs[k])))
+        remeasured.append(xs[k])
+    return (*slope_fit(xs, ys), remeasured)
+
+
 def ref_gpu_timing(scene, w, h, bounces, lpp):
     """The reference's sm_100a GPU build on the same box (north_star's comparison target). Its `GPU Took` timer
     (raytracing.cu:172,279-281) includes ~13 cudaMalloc / cudaFree, the pageable scene upload and the download, which do not
@@ -249,30 +277,7 @@ def ref_gpu_timing(scene, w, h, bounces, lpp):
             if any(y is None for y in ys):
                 out[mode] = {"unavailable": "no `GPU Took` line"}
                 continue
-            n = len(pts)
-            mx = sum(pts) / n
-            sxx = sum((x - mx) ** 2 for x in pts)
-
-            def fit():
-                my = sum(ys) / n
-                slope = sum((x - mx) * (y - my) for x, y in zip(pts, ys)) / sxx
-                icpt = my - slope * mx
-                return slope, icpt, [y - (icpt + slope * x) for x, y in zip(pts, ys)]
-
-            # The timer's noise is one-sided (an allocation or the upload taking longer): a point that sits ABOVE the line by
-            # more than 3 x the median residual and 2 % of its value is run three more times (best kept), at most twice.
-            remeasured = []
-            for _ in range(2):
-                slope, icpt, res = fit()
-                k = max(range(n), key=lambda j: res[j])
-                med = sorted(abs(r) for r in res)[n // 2]
-                if res[k] <= max(3.0 * med, 0.02 * ys[k]):
-                    break
-                again = [t for t in (took(pts[k], flags) for _ in range(3)) if t]
-                ys[k] = min([ys[k]] + again)
-                remeasured.append(pts[k])
-            slope, icpt, res = fit()
-            se = (sum(r * r for r in res) / max(1, n - 2) / sxx) ** 0.5
+            slope, icpt, res, se, remeasured = fit_with_remeasure(pts, ys, lambda spp: [t for t in (took(spp, flags) for _ in range(3)) if t])
             rate = lpp * w * h / max(slope, 1e-12) * 1e-6
             out[mode] = {"value": rate, "unit": "Mrays/s", "spread": rate * se / max(slope, 1e-12), "spread_rel": se / max(slope, 1e-12),
                          "s_per_spp": slope, "fixed_cost_s": icpt, "max_residual_s": max(abs(r) for r in res), "gpu_took_s": dict(zip(pts, ys)),

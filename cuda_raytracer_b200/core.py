@@ -153,10 +153,17 @@ def lib():
 
 
 def build_id():
-    """sha1 of the loaded librtcore.so: ties an ncu capture (profiles/*_traffic.json) to the binary a bench line ran."""
+    """Identifies the build an ncu capture (profiles/*_traffic.json) or a bench line ran. For the in-tree library: "src-" + the
+    sha1 the Makefile writes next to it (librtcore.srcid: sources + compile flags) — nvcc's output is not byte-reproducible, so
+    two builds of the same tree have different binaries but the same id. For a library selected with RT_LIBRTCORE (A/B
+    variants built with extra -D flags), or without that file: "bin-" + the sha1 of the binary."""
     import hashlib
+    default = os.path.join(os.path.dirname(os.path.abspath(__file__)), "librtcore.so")
+    stamp = os.path.join(os.path.dirname(default), "librtcore.srcid")
+    if os.path.abspath(LIB_PATH) == default and os.path.exists(stamp):
+        return "src-" + open(stamp).read().strip()
     with open(LIB_PATH, "rb") as f:
-        return hashlib.sha1(f.read()).hexdigest()[:16]
+        return "bin-" + hashlib.sha1(f.read()).hexdigest()[:16]
 
 
 def _check(rc, ctx=None):
