@@ -234,13 +234,24 @@ def slope_fit(xs, ys):
     return slope, icpt, res, se
 
 
+def robust_line(xs, ys):
+    """Theil-Sen line: median of the pairwise slopes, median intercept. One bad point in five does not move it."""
+    sl = sorted((ys[j] - ys[i]) / (xs[j] - xs[i]) for i in range(len(xs)) for j in range(i + 1, len(xs)))
+    slope = sl[len(sl) // 2] if len(sl) % 2 else 0.5 * (sl[len(sl) // 2 - 1] + sl[len(sl) // 2])
+    ic = sorted(y - slope * x for x, y in zip(xs, ys))
+    icpt = ic[len(ic) // 2] if len(ic) % 2 else 0.5 * (ic[len(ic) // 2 - 1] + ic[len(ic) // 2])
+    return slope, icpt
+
+
 def fit_with_remeasure(xs, ys, measure_again, rounds=2):
     """slope_fit for a timer whose noise is one-sided (an allocation or an upload taking longer, never shorter): a point that sits
-    ABOVE the line by more than 3 x the median absolute residual and 2 % of its value is measured again (`measure_again(x)`
-    returns further samples, the smallest is kept), at most `rounds` times. Modifies ys; returns the fit + the re-measured xs."""
+    ABOVE the robust (Theil-Sen) line by more than 3 x the median absolute residual to that line and 2 % of its value is
+    measured again (`measure_again(x)` returns further samples, the smallest is kept), at most `rounds` times. The reported
+    fit is the least-squares one of the final points. Modifies ys; returns the fit + the re-measured xs."""
     remeasured = []
     for _ in range(rounds):
-        slope, icpt, res, se = slope_fit(xs, ys)
+        slope, icpt = robust_line(xs, ys)
+        res = [y - (icpt + slope * x) for x, y in zip(xs, ys)]
         k = max(range(len(xs)), key=lambda j: res[j])
         med = sorted(abs(r) for r in res)[len(xs) // 2]
         if res[k] <= max(3.0 * med, 0.02 * ys[k]):
@@ -255,7 +266,8 @@ def ref_gpu_timing(scene, w, h, bounces, lpp):
     (raytracing.cu:172,279-281) includes ~13 cudaMalloc / cudaFree, the pageable scene upload and the download, which do not
     depend on the sample count; the steady-state rate is therefore the least-squares SLOPE of `GPU Took` over five sample
     counts (whole passes of 20), every point the best of three runs after one discarded warm-up run per mode. Reported with
-    the standard error of the slope (`spread`) and the largest residual, so that a noisy box shows."""
+    the standard error of the slope (`spread`) and the largest residual, so that a noisy box shows. The timer's hiccups only
+    ever ADD time: a point that stands above the robust line through the five is run three more times (fit_with_remeasure)."""
     # sample counts far enough apart that the slope stands clear of the timer's ~20 ms run-to-run jitter (spheres at 1000x1000: 0.2 ms per spp)
     pts = (200, 600, 1000, 1400, 1800) if w * h <= 1_000_000 else (20, 40, 60, 80, 100)
     paths = {spp: _scene_file_with_image(scene, w, h, spp, bounces) for spp in pts}

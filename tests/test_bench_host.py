@@ -59,6 +59,11 @@ def test_one_sided_outlier_is_measured_again():
     slope, icpt, res, se, re_x = bench.fit_with_remeasure(xs, ys, again)
     assert asked == [60] and re_x == [60] and ys[2] == 0.84
     assert se / slope < 0.05
+    # the sort-mode series of the next run: least squares alone is pulled up by the bad point (residual 0.114 against a median
+    # of 0.043) and would not have flagged it
+    ys = [0.503434, 0.649788, 0.780731, 1.1003, 1.08669]
+    *_, se2, re_x = bench.fit_with_remeasure(xs, ys, lambda x: [0.94, 0.95])
+    assert re_x == [80] and ys[3] == 0.94
     # a clean series asks for nothing
     ys = [0.3 + 0.008 * x + d for x, d in zip(xs, (0.001, -0.002, 0.0015, -0.001, 0.0005))]
     *_, re_x = bench.fit_with_remeasure(xs, ys, lambda x: pytest.fail("should not re-measure"))
