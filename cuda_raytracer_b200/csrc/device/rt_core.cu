@@ -1011,24 +1011,69 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     // member of a wave of whole passes with the same samples per pixel (the member index of a ray is id / pass_rays, which needs
     // full-size members in front). On its own it would be a whole chain of latency-bound launches for a fraction of a pass: a
     // quarter pass as its own wave cost teapot's 8-GPU share 2 ms of 19 (profiles/r2f_partial.md).
+    // The waves of a run of equal passes are made EQUAL in size (50 passes with room for 16: 13 + 13 + 12 + 12, not 16 + 16 + 16 + 2;
+    // 6 passes + a partial one on three pipes: 2 + 2 + (2 + partial), not (2 + partial) + 3 + 1), their number a multiple of the
+    // pipes where that fits, and the partial passes ride on the smallest waves: the pipes then finish together, and the call ends
+    // with the chains of several waves overlapping instead of the longest wave's alone (lamp 1000x1000 on 8 GPUs: the ranks whose
+    // share was 3 + (2 + partial) + 1 took 1-2 ms of 32 longer than the others, profiles/r2g_waves.md).
     std::stable_partition(segs.begin(), segs.end(), whole);
     const int n_whole = (int)(std::find_if(segs.begin(), segs.end(), [&](const Segment &g) { return !whole(g); }) - segs.begin());
-    int wi = 0, pi = n_whole;  // next whole pass, next partial pass
-    while (wi < n_whole || pi < n_segs) {
+    struct WavePlan {
         Segment member[kMaxPassGroup];
-        int group = 0, partial_member = -1;
-        if (wi < n_whole) {
-            const int spp0 = spp_of(segs[wi].pass);
-            const int room = std::max(1, max_group - (pi < n_segs ? 1 : 0));  // keep a slot for a partial pass that is waiting
-            while (group < room && wi < n_whole && spp_of(segs[wi].pass) == spp0) member[group++] = segs[wi++];
-            if (pi < n_segs && group < max_group && spp_of(segs[pi].pass) == spp0 && (size_t)segs[pi].count < pixels * (size_t)spp0) {
-                partial_member = group;
-                member[group++] = segs[pi++];
-            }
-        } else {  // only partial passes are left: each is a wave of its own
-            partial_member = 0;
-            member[group++] = segs[pi++];
+        int group, partial_member;
+    };
+    std::vector<WavePlan> plan;
+    std::vector<char> rides(n_segs, 0);  // partial passes that found a wave
+    for (int wi = 0; wi < n_whole;) {
+        const int spp0 = spp_of(segs[wi].pass);
+        int run = 0;
+        while (wi + run < n_whole && spp_of(segs[wi + run].pass) == spp0) run++;
+        std::vector<int> riders;  // partial passes that can ride with this run, largest first
+        for (int j = n_whole; j < n_segs; j++)
+            if (!rides[j] && spp_of(segs[j].pass) == spp0 && (size_t)segs[j].count < pixels * (size_t)spp0) riders.push_back(j);
+        std::stable_sort(riders.begin(), riders.end(), [&](int x, int y) { return segs[x].count > segs[y].count; });
+        // W waves: wave k holds run / W whole passes (+ 1 for the first run % W waves); the last P waves carry one rider each
+        auto fits = [&](int W, int P) {
+            if (W < 1 || W > run || P > W) return false;
+            for (int k = 0; k < W; k++)
+                if (run / W + (k < run % W ? 1 : 0) + (k >= W - P ? 1 : 0) > max_group) return false;
+            return true;
+        };
+        int W = run, P = 0;
+        for (int p = std::min<int>((int)riders.size(), run); p >= 0; p--) {  // drop riders that do not fit (wave size 1)
+            int first = 0;
+            for (int w = 1; w <= run && !first; w++) if (fits(w, p)) first = w;
+            if (!first) continue;
+            W = first;
+            P = p;
+            const int up = (W + pipes - 1) / pipes * pipes;
+            if (W > 1 && up != W && fits(up, p)) W = up;
+            break;
         }
+        for (int k = 0; k < W; k++) {
+            WavePlan wp{};
+            const int n = run / W + (k < run % W ? 1 : 0);
+            for (int m = 0; m < n; m++) wp.member[wp.group++] = segs[wi++];
+            wp.partial_member = -1;
+            if (k >= W - P) {  // the last wave (the smallest) takes the largest rider
+                const int j = riders[W - 1 - k];
+                rides[j] = 1;
+                wp.partial_member = wp.group;
+                wp.member[wp.group++] = segs[j];
+            }
+            plan.push_back(wp);
+        }
+    }
+    for (int j = n_whole; j < n_segs; j++)  // partial passes without company: each is a wave of its own
+        if (!rides[j]) {
+            WavePlan wp{};
+            wp.member[wp.group++] = segs[j];
+            wp.partial_member = 0;
+            plan.push_back(wp);
+        }
+    for (const WavePlan &wp : plan) {
+        const Segment *member = wp.member;
+        const int group = wp.group, partial_member = wp.partial_member;
         const int rays_to_cast = spp_of(member[0].pass);
         const bool partial = partial_member >= 0;
         const Segment &pseg = member[partial ? partial_member : 0];
