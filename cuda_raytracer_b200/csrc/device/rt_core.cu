@@ -1011,11 +1011,12 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     // member of a wave of whole passes with the same samples per pixel (the member index of a ray is id / pass_rays, which needs
     // full-size members in front). On its own it would be a whole chain of latency-bound launches for a fraction of a pass: a
     // quarter pass as its own wave cost teapot's 8-GPU share 2 ms of 19 (profiles/r2f_partial.md).
-    // The waves of a run of equal passes are made EQUAL in size (50 passes with room for 16: 13 + 13 + 12 + 12, not 16 + 16 + 16 + 2;
-    // 6 passes + a partial one on three pipes: 2 + 2 + (2 + partial), not (2 + partial) + 3 + 1), their number a multiple of the
-    // pipes where that fits, and the partial passes ride on the smallest waves: the pipes then finish together, and the call ends
-    // with the chains of several waves overlapping instead of the longest wave's alone (lamp 1000x1000 on 8 GPUs: the ranks whose
-    // share was 3 + (2 + partial) + 1 took 1-2 ms of 32 longer than the others, profiles/r2g_waves.md).
+    // A run of equal passes that needs MORE waves than there are pipes is dealt out evenly (50 passes with room for 16: 13 + 13 + 12
+    // + 12, not 16 + 16 + 16 + 2; wave count a multiple of the pipes where that fits), so that the pipes finish together: teapot
+    // 1000x1000 whole frame 130.3 -> 128.7 ms, lamp 1000x1000 240.4 -> 238.2. A run that fits ONE round of waves keeps the
+    // first-fit plan (6 passes + a partial one on three pipes: (2 + partial) + 3 + 1): there the unequal waves help, because the
+    // short waves' chains of late bounces run while the long wave still has bulk work (teapot's share of 8: 17.09 ms first-fit,
+    // 17.44 ms as 2 + 2 + (2 + partial); profiles/r2g_waves.md).
     std::stable_partition(segs.begin(), segs.end(), whole);
     const int n_whole = (int)(std::find_if(segs.begin(), segs.end(), [&](const Segment &g) { return !whole(g); }) - segs.begin());
     struct WavePlan {
@@ -1032,6 +1033,26 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
         for (int j = n_whole; j < n_segs; j++)
             if (!rides[j] && spp_of(segs[j].pass) == spp0 && (size_t)segs[j].count < pixels * (size_t)spp0) riders.push_back(j);
         std::stable_sort(riders.begin(), riders.end(), [&](int x, int y) { return segs[x].count > segs[y].count; });
+        const int P0 = max_group >= 2 ? std::min<int>((int)riders.size(), run) : 0;
+        if ((run + P0 + max_group - 1) / max_group <= pipes) {
+            // one round: first fit, in queue order; a slot is kept for a rider while one is waiting
+            std::stable_sort(riders.begin(), riders.end());
+            size_t next_rider = 0;
+            for (int left = run; left > 0;) {
+                WavePlan wp{};
+                const int room = std::max(1, max_group - (next_rider < riders.size() ? 1 : 0));
+                while (wp.group < room && left > 0) { wp.member[wp.group++] = segs[wi++]; left--; }
+                wp.partial_member = -1;
+                if (next_rider < riders.size() && wp.group < max_group) {
+                    const int j = riders[next_rider++];
+                    rides[j] = 1;
+                    wp.partial_member = wp.group;
+                    wp.member[wp.group++] = segs[j];
+                }
+                plan.push_back(wp);
+            }
+            continue;
+        }
         // W waves: wave k holds run / W whole passes (+ 1 for the first run % W waves); the last P waves carry one rider each
         auto fits = [&](int W, int P) {
             if (W < 1 || W > run || P > W) return false;
@@ -1040,7 +1061,7 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
             return true;
         };
         int W = run, P = 0;
-        for (int p = std::min<int>((int)riders.size(), run); p >= 0; p--) {  // drop riders that do not fit (wave size 1)
+        for (int p = P0; p >= 0; p--) {  // drop riders that do not fit
             int first = 0;
             for (int w = 1; w <= run && !first; w++) if (fits(w, p)) first = w;
             if (!first) continue;
