@@ -222,6 +222,22 @@ def reference_arm(args, rank, world, emit):
 
 
 # ---- the B200 arm ------------------------------------------------------------------------------------------------------
+def agreeing_runs(measure, least=3, most=7, tol=0.02):
+    """Samples of a timer with one-sided noise: at least `least`, then more until the two smallest agree to `tol` (or `most` runs).
+    The smallest is the estimate; a single lucky-looking outlier downwards does not exist for such a timer."""
+    runs, tries = [], 0
+    while len(runs) < most and tries < most + 2:
+        tries += 1
+        t = measure()
+        if t:
+            runs.append(t)
+        if len(runs) >= least:
+            lo = sorted(runs)
+            if lo[1] <= lo[0] * (1.0 + tol):
+                break
+    return runs
+
+
 def slope_fit(xs, ys):
     """Least-squares line through (xs, ys): slope, intercept, residuals, standard error of the slope."""
     n = len(xs)
@@ -277,15 +293,16 @@ def ref_gpu_timing(scene, w, h, bounces, lpp):
         m = re.search(r"GPU Took ([0-9.eE+-]+)s", o)
         return float(m.group(1)) if m else None
 
-    out = {"config": f"{scene}.scene {w}x{h}, `GPU Took` at {list(pts)} spp, best of 3 per point, least-squares slope = steady state"}
+    out = {"config": f"{scene}.scene {w}x{h}, `GPU Took` at {list(pts)} spp, per point the smallest of 3-7 runs (until the two smallest agree to 2 %), least-squares slope = steady state"}
     try:
         for flags in ((), ("no_sort",)):
             mode = "no_sort" if flags else "sort"
             took(pts[0], flags)  # warm-up, discarded
-            ys = []
+            ys, n_runs = [], []
             for spp in pts:
-                runs = [t for t in (took(spp, flags) for _ in range(3)) if t]
+                runs = agreeing_runs(lambda: took(spp, flags))
                 ys.append(min(runs) if runs else None)
+                n_runs.append(len(runs))
             if any(y is None for y in ys):
                 out[mode] = {"unavailable": "no `GPU Took` line"}
                 continue
@@ -293,16 +310,18 @@ def ref_gpu_timing(scene, w, h, bounces, lpp):
             rate = lpp * w * h / max(slope, 1e-12) * 1e-6
             out[mode] = {"value": rate, "unit": "Mrays/s", "spread": rate * se / max(slope, 1e-12), "spread_rel": se / max(slope, 1e-12),
                          "s_per_spp": slope, "fixed_cost_s": icpt, "max_residual_s": max(abs(r) for r in res), "gpu_took_s": dict(zip(pts, ys)),
-                         "remeasured_spp": remeasured}
+                         "runs_per_point": n_runs, "remeasured_spp": remeasured}
     finally:
         for pth in paths.values():
             os.unlink(pth)
     return out
 
 
-def newest_ncu_summary(build=None):
-    """The ncu summary (profiles/r*_traffic.json, written by tools/ncu_summary.py) of THIS build if there is one, else the one
-    with the highest name (= the latest capture; bench.py then reports it as stale and leaves the derived keys out)."""
+def newest_ncu_summary(build=None, kernels=None):
+    """The ncu summary (profiles/r*_traffic.json, written by tools/ncu_summary.py) that measured THIS library's kernels: the
+    newest one whose `kernel_id` (sha1 of the SASS of trace_rays_kernel / shade_kernel, core.kernel_id()) or `build_id` (hash of
+    the sources) equals the running library's; else the one with the highest name (= the latest capture; bench.py then
+    reports it as stale and leaves the derived keys out)."""
     found = []
     for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_traffic.json"))):
         try:
@@ -314,7 +333,7 @@ def newest_ncu_summary(build=None):
         d["_file"] = os.path.relpath(f, ROOT)
         found.append(d)
     f32 = [d for d in found if "nodes=f32" in d.get("workload", "")]  # the default node format's captures
-    same = [d for d in f32 if d.get("build_id") == build]
+    same = [d for d in f32 if d.get("build_id") == build or (kernels is not None and d.get("kernel_id") == kernels)]
     return (same or f32 or found or [None])[-1]
 
 
@@ -340,7 +359,7 @@ def main():
     import torch
 
     import cuda_raytracer_b200 as rt
-    from cuda_raytracer_b200.core import build_id
+    from cuda_raytracer_b200.core import build_id, kernel_id
     from cuda_raytracer_b200.multi_gpu import DeviceFramebuffer as _DevBuf, sample_range
 
     if not torch.cuda.is_available():
@@ -519,13 +538,17 @@ def main():
                 "timing_note": "kernel durations: CUDA event pairs around every launch in %d attribution step(s) run right after the timed region "
                                "(one wave at a time, %.1f ms per step); the timed region itself runs two waves at a time on two streams, where "
                                "per-kernel intervals would overlap" % (args.steps, attr_s / args.steps * 1e3)}
-    ncu = newest_ncu_summary(build_id())
+    ncu = newest_ncu_summary(build_id(), kernel_id())
     if ncu is not None:
+        # the capture counts for this run if it measured the same machine code: same sources, or the same SASS of the two kernels
+        # (a host-only change gives a new source hash and leaves the kernels alone)
+        same_kernels = kernel_id() is not None and ncu.get("kernel_id") == kernel_id()
         same_build = ncu.get("build_id") == build_id()
         roofline["ncu_source"] = {"file": ncu["_file"], "raw_csv": ncu.get("raw_csv"), "build_id": ncu.get("build_id"), "this_build_id": build_id(),
+                                  "kernel_id": ncu.get("kernel_id"), "this_kernel_id": kernel_id(), "same_kernels": same_kernels,
                                   "same_build": same_build, "workload": ncu.get("workload")}
         tk, sk = ncu.get("trace_rays_kernel", {}), ncu.get("shade_kernel", {})
-        if same_build and args.workload == "lamp_4k" and not sort and tk:
+        if (same_build or same_kernels) and args.workload == "lamp_4k" and not sort and tk:
             # per live ray-bounce figures of the capture x this run's ray-bounces / this run's kernel time
             roofline["traffic"] = tk["dram_bytes_per_live_ray_bounce"] * live_rank0 / n_trace_launches
             roofline["traffic_note"] = "DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) per average trace launch"
@@ -540,13 +563,13 @@ def main():
                                             "dram_frac": sk["dram_bytes_per_live_ray_bounce"] * live_rank0 / shade_s * 1e-9 / peak,
                                             "l2_frac": sk["lts_bytes_per_live_ray_bounce"] * live_rank0 / shade_s * 1e-9 / l2_peak,
                                             **{k: sk[k] for k in ("l1_wavefront_pct", "issue_active", "lanes_per_inst") if k in sk}}
-        elif not same_build:
-            roofline["traffic_note"] = "the newest ncu capture under profiles/ is of another build: traffic and the per-level fractions are left out"
+        elif not (same_build or same_kernels):
+            roofline["traffic_note"] = "the newest ncu capture under profiles/ is of other kernels: traffic and the per-level fractions are left out"
     line = {
         "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dev_s / args.steps * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": config_for(args), "run": {"pass_group": args.pass_group or "auto (70 % of free memory)", "nodes": r.node_mode, "build_id": build_id()},
+        "config": config_for(args), "run": {"pass_group": args.pass_group or "auto (70 % of free memory)", "nodes": r.node_mode, "build_id": build_id(), "kernel_id": kernel_id()},
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_step": e2e_s / args.steps * 1e3,
                 "h2d_bytes_per_step": int(scene_bytes), "d2h_bytes_per_step": int(n_floats * 4),
                 "ms_each": [round(t * 1e3, 2) for t in e2e_t], "upload_ms_each": [round(t * 1e3, 2) for t in e2e_upload[-len(e2e_t):]]},

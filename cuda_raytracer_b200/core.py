@@ -166,6 +166,37 @@ def build_id():
         return "bin-" + hashlib.sha1(f.read()).hexdigest()[:16]
 
 
+_KERNEL_ID = {}
+
+
+def kernel_id(pattern="trace_rays_kernel|shade_kernel"):
+    """sha1 of the SASS (``cuobjdump -sass``) of the loaded library's kernels whose names match ``pattern`` — the identity of the
+    machine code an ncu capture measured. It is the same for two builds of the same device code (host-only changes and nvcc's
+    non-reproducible symbol ids leave it alone) and changes with any instruction of those kernels. None without cuobjdump."""
+    import hashlib
+    import re
+    import shutil
+    import subprocess
+    if pattern in _KERNEL_ID:
+        return _KERNEL_ID[pattern]
+    tool = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    kid = None
+    try:
+        out = subprocess.run([tool, "-sass", LIB_PATH], capture_output=True, text=True, timeout=120, check=True).stdout
+        keep, picked, rx = False, [], re.compile(pattern)
+        for line in out.splitlines():
+            if "Function : " in line:
+                keep = bool(rx.search(line))
+            if keep:
+                picked.append(line)
+        if picked:
+            kid = "sass-" + hashlib.sha1(("\n".join(picked) + "\n").encode()).hexdigest()[:16]
+    except (OSError, subprocess.SubprocessError):
+        kid = None
+    _KERNEL_ID[pattern] = kid
+    return kid
+
+
 def _check(rc, ctx=None):
     if rc != RT_OK:
         msg = lib().rt_last_error(ctx)

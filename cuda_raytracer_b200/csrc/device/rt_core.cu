@@ -948,7 +948,10 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     // fixed chain of late bounces is a tenth of it, and three smaller waves leave less of that chain without company than two
     // (teapot 1000x1000, samples [0, 125): 17.67 ms on 2 pipes, 17.11 on 3, 17.25 on 4; profiles/r2f_partial.md). Whole frames
     // measured no gain from a third pipe (profiles/r1k_box_ch.md).
-    const int want_pipes = ctx->pipes > 0 ? ctx->pipes : (n_segs <= 8 ? 3 : 2);
+    // Only where the whole call then fits ONE round of three waves in memory: lamp 4K's share of 4 GPUs is 8 passes of 14.6 GB with
+    // room for 8 at a time, which is two pipes of 4 + 4, not three pipes of 2 + 2 + 1 + 1 + 1 + 1.
+    const bool small_call = n_segs <= 8 && mem_group / 3 >= (n_segs + 2) / 3;
+    const int want_pipes = ctx->pipes > 0 ? ctx->pipes : (small_call ? 3 : 2);
     int pipes = (sort || timing || collect || opts.single_pipe || n_segs < 2) ? 1 : want_pipes;
     pipes = std::max(1, std::min(pipes, n_segs));
     // automatic wave size with several pipes: the work split evenly over the pipes (rounded UP: 5 passes on 2 pipes are waves of

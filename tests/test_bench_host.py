@@ -77,6 +77,16 @@ def test_one_sided_outlier_is_measured_again():
     assert 60 not in calls
 
 
+def test_agreeing_runs_keeps_sampling_a_noisy_point():
+    it = iter([1.38, 1.21, 1.30, 1.135, 1.14, 9.0])
+    runs = bench.agreeing_runs(lambda: next(it))
+    assert runs == [1.38, 1.21, 1.30, 1.135, 1.14] and min(runs) == 1.135   # stopped once 1.135 and 1.14 agreed
+    it = iter([0.50, 0.505, 0.51, 9.0])
+    assert bench.agreeing_runs(lambda: next(it)) == [0.50, 0.505, 0.51]     # quiet point: three runs
+    it = iter([None, 0.5, None, 0.7, 0.9, 1.1, 1.3, 1.5, 1.7, 1.9, 2.1])
+    assert len(bench.agreeing_runs(lambda: next(it))) <= 7                  # never agrees: bounded
+
+
 def test_ncu_summary_of_the_running_build_is_preferred(tmp_path, monkeypatch):
     prof = tmp_path / "profiles"
     prof.mkdir()
@@ -88,6 +98,11 @@ def test_ncu_summary_of_the_running_build_is_preferred(tmp_path, monkeypatch):
     assert bench.newest_ncu_summary("bbbb")["_file"].endswith("r2b_f32_traffic.json")  # the default node format's capture
     stale = bench.newest_ncu_summary("cccc")
     assert stale["build_id"] == "bbbb" and "f32" in stale["workload"]      # reported as stale by main(): same_build false
+    # a host-only change: new source hash, same SASS of the captured kernels -> the capture of those kernels still counts
+    json.dump({"build_id": "dddd", "kernel_id": "sass-1", "workload": "lamp nodes=f32", "trace_rays_kernel": {}}, open(prof / "r2a_zz_traffic.json", "w"))
+    assert bench.newest_ncu_summary("eeee", "sass-1")["build_id"] == "dddd"
+    assert bench.newest_ncu_summary("eeee", "sass-2")["build_id"] == "bbbb"
+    assert bench.newest_ncu_summary("eeee", None)["build_id"] == "bbbb"
 
 
 def test_committed_capture_matches_the_committed_library_when_present():
@@ -96,8 +111,9 @@ def test_committed_capture_matches_the_committed_library_when_present():
     so = os.path.join(ROOT, "cuda_raytracer_b200", "librtcore.so")
     if not os.path.exists(so):
         pytest.skip("librtcore.so not built")
-    from cuda_raytracer_b200.core import build_id
-    d = bench.newest_ncu_summary(build_id())
+    from cuda_raytracer_b200.core import build_id, kernel_id
+    d = bench.newest_ncu_summary(build_id(), kernel_id())
     assert d is not None
-    if d["build_id"] != build_id():
-        pytest.skip(f"capture {d['_file']} is of build {d['build_id']}, library is {build_id()}: bench.py will leave the per-level keys out")
+    if d["build_id"] != build_id() and (kernel_id() is None or d.get("kernel_id") != kernel_id()):
+        pytest.skip(f"capture {d['_file']} is of build {d['build_id']} / kernels {d.get('kernel_id')}, library is {build_id()} / {kernel_id()}: "
+                    "bench.py will leave the per-level keys out")

@@ -86,7 +86,7 @@ def main():
             d["class"], d["bounce"], d["live_rays"] = cls, b, live[b] if b < len(live) else 0
             w.writerow({k: d.get(k) for k in fields})
             per_class.setdefault(cls, []).append(d)
-    summary = {"build_id": target["build_id"], "workload": target["workload"], "raw_csv": os.path.relpath(raw_path, ROOT),
+    summary = {"build_id": target["build_id"], "kernel_id": target.get("kernel_id"), "workload": target["workload"], "raw_csv": os.path.relpath(raw_path, ROOT),
                "source": f"ncu --set full --clock-control none of `{target['command']}`; launches of bounces 0..{max(counters.values()) - 1} of one pass "
                          "(they hold the %.1f %% of the pass's live ray-bounces that the per-ray figures are taken over)" %
                          (100.0 * sum(live[:max(counters.values())]) / max(1, sum(live))),
