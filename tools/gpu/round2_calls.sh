@@ -352,5 +352,8 @@ timeout 400 python -m pytest tests -q -m gpu -x > gpurun_out/c29_tests.log 2>&1
 echo "tests rc=$?" >> gpurun_out/c29_tests.log
 timeout 120 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/c29_smoke.log 2>&1
 ;;
-*) echo "usage: $0 <call>: 01 02 03 03s 04 05 06 07 08 09 10 11 12 13 14 15 16 17 18 19 20 21 22 23 24 25 26 27 28 29"; exit 2 ;;
+30)  # lamp 1000x1000: per-bounce and per-pass kernel times of rank 0's and rank 3's share of 8 (why rank 3 is 1.7 ms slower)
+timeout 150 python tools/share_bounces.py lamp 1000 1000 1000 10 8 0 3 > gpurun_out/c30_share_bounces.log 2>&1
+;;
+*) echo "usage: $0 <call>: 01 02 03 03s 04 05 06 07 08 09 10 11 12 13 14 15 16 17 18 19 20 21 22 23 24 25 26 27 28 29 30"; exit 2 ;;
 esac
