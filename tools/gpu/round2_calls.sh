@@ -355,5 +355,10 @@ timeout 120 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')
 30)  # lamp 1000x1000: per-bounce and per-pass kernel times of rank 0's and rank 3's share of 8 (why rank 3 is 1.7 ms slower)
 timeout 150 python tools/share_bounces.py lamp 1000 1000 1000 10 8 0 3 > gpurun_out/c30_share_bounces.log 2>&1
 ;;
-*) echo "usage: $0 <call>: 01 02 03 03s 04 05 06 07 08 09 10 11 12 13 14 15 16 17 18 19 20 21 22 23 24 25 26 27 28 29 30"; exit 2 ;;
+31)  # last source: kernel id on the box (cuobjdump there) and a short bench line whose roofline keys come from the r2h capture
+python -c "from cuda_raytracer_b200.core import kernel_id, build_id; print(kernel_id(), build_id())" > gpurun_out/c31_ids.log 2>&1
+timeout 200 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-ref-gpu --no-extras > gpurun_out/c31_bench.json 2> gpurun_out/c31_bench.err
+echo "bench rc=$?" >> gpurun_out/c31_bench.err
+;;
+*) echo "usage: $0 <call>: 01 02 03 03s 04 05 06 07 08 09 10 11 12 13 14 15 16 17 18 19 20 21 22 23 24 25 26 27 28 29 30 31"; exit 2 ;;
 esac
