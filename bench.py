@@ -546,7 +546,10 @@ def main():
         same_build = ncu.get("build_id") == build_id()
         roofline["ncu_source"] = {"file": ncu["_file"], "raw_csv": ncu.get("raw_csv"), "build_id": ncu.get("build_id"), "this_build_id": build_id(),
                                   "kernel_id": ncu.get("kernel_id"), "this_kernel_id": kernel_id(), "same_kernels": same_kernels,
-                                  "same_build": same_build, "workload": ncu.get("workload")}
+                                  "same_build": same_build, "valid_for_this_run": bool(same_build or same_kernels),
+                                  "validity_rule": "same sources (build_id) or byte-identical SASS of trace_rays_kernel* / shade_kernel* (kernel_id): "
+                                                   "a host-only change moves build_id and leaves the captured kernels alone",
+                                  "workload": ncu.get("workload")}
         tk, sk = ncu.get("trace_rays_kernel", {}), ncu.get("shade_kernel", {})
         if (same_build or same_kernels) and args.workload == "lamp_4k" and not sort and tk:
             # per live ray-bounce figures of the capture x this run's ray-bounces / this run's kernel time
