@@ -76,6 +76,7 @@ EXPORTS = [
     "rt_render", "rt_render_device", "rt_postprocess", "rt_framebuffer_upload", "rt_trace_closest", "rt_generate_rays",
     "rt_process_rays", "rt_sort_pairs", "rt_sort_pairs_static", "rt_scene_download_bvh", "rt_scene_bvh_device_ms", "rt_sort_device_ms", "rt_index_divide",
     "rt_probe_copy_gbs",
+    "rt_plan_waves",
     "rt_multi_create", "rt_multi_destroy", "rt_multi_device_count", "rt_multi_last_error", "rt_multi_context", "rt_multi_set_node_mode",
     "rt_multi_scene_upload", "rt_multi_render", "rt_multi_reduce_ms", "rt_multi_postprocess",
     # rt_scene.h
@@ -123,6 +124,7 @@ def lib():
     L.rt_sort_device_ms.argtypes = [vp]
     L.rt_sort_device_ms.restype = C.c_double
     L.rt_probe_copy_gbs.argtypes = [vp, C.c_int64, C.c_int32, C.POINTER(C.c_double)]
+    L.rt_plan_waves.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int64]
     L.rt_index_divide.argtypes = [C.c_uint32, C.c_uint32]
     L.rt_index_divide.restype = C.c_uint32
     L.rt_multi_create.argtypes = [C.POINTER(vp), C.POINTER(C.c_int), C.c_int]
@@ -164,6 +166,27 @@ def build_id():
         return "src-" + open(stamp).read().strip()
     with open(LIB_PATH, "rb") as f:
         return "bin-" + hashlib.sha1(f.read()).hexdigest()[:16]
+
+
+def plan_waves(width, height, ray_count, max_group, pipes, pass_spp=0, pass_first=0, pass_count=0, ray_first=0, ray_range=0,
+               sample_first=0, sample_count=0):
+    """rt_plan_waves (host only): the waves rt_render would form, as a list of (members, partial_member) with members =
+    list of (pass, offset, count, sub_first, sub_count). ``ray_range`` is rt_render_opts.ray_count."""
+    o = Renderer._opts(False, pass_spp, pass_first, pass_count, False, 0, 0, ray_first=ray_first, ray_count=ray_range,
+                       sample_first=sample_first, sample_count=sample_count)
+    passes = (ray_count + (pass_spp or 20) - 1) // (pass_spp or 20)
+    cap = 7 * (passes + 4) + 64
+    out = (C.c_int64 * cap)()
+    n = lib().rt_plan_waves(C.byref(o), width, height, ray_count, max_group, pipes, out, cap)
+    if n < 0:
+        raise RtError(n, "rt_plan_waves: option out of range")
+    waves, at = [], 0
+    for _ in range(n):
+        group, partial = int(out[at]), int(out[at + 1])
+        at += 2
+        waves.append(([tuple(int(v) for v in out[at + 5 * m: at + 5 * m + 5]) for m in range(group)], partial))
+        at += 5 * group
+    return waves
 
 
 _KERNEL_ID = {}

@@ -16,6 +16,7 @@
 #include "bvh_build.cuh"
 #include "kernels.cuh"
 #include "radix_sort.cuh"
+#include "wave_plan.cuh"
 #include "wide_nodes.cuh"
 
 namespace rt {
@@ -857,43 +858,15 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     const int pass_spp = opts.pass_spp > 0 ? opts.pass_spp : 20;  // MAX_RAYS_PER_PIXEL_PER_PASS, raytracing.cu:109
     const size_t pixels = (size_t)ctx->ds.width * ctx->ds.height;
     if (pixels * (size_t)pass_spp >= (1ull << 31)) return fail(ctx, RT_ERR_INVALID, "rt_render: width*height*pass_spp must be < 2^31");
-    const int total_passes = (ctx->ray_count + pass_spp - 1) / pass_spp;
-    // The work of this call: SEGMENTS = rays [offset, offset + count) of a pass. Whole passes by default or by pass range; with
-    // ray_count > 0 a range of the frame's ray sequence, whose first and last pass may be partial (seeds are functions of
-    // the pass and the ray's index inside it: raytracing.cu:89,229,236, scene.cu:81).
-    struct Segment {
-        int pass;
-        uint32_t offset, count;         // rays [offset, offset + count) of the pass; strided: count = pixels x sub_count
-        uint32_t sub_first, sub_count;  // sub_count > 0: samples [sub_first, sub_first + sub_count) of every pixel
-    };
+    // The work of this call: SEGMENTS = rays [offset, offset + count) of a pass (wave_plan.cuh): whole passes by default or by pass
+    // range; with sample_count / ray_count > 0 a range of every pixel's samples / of the frame's ray sequence, whose first and
+    // last pass may be partial.
+    using Segment = PassSegment;
+    const FrameShape shape{pixels, ctx->ray_count, pass_spp};
     std::vector<Segment> segs;
-    auto spp_of = [&](int p) { return std::min(ctx->ray_count - p * pass_spp, pass_spp); };
-    if (opts.sample_count > 0) {  // samples [s0, s1) of every pixel: pass p holds samples [p * pass_spp, p * pass_spp + spp_of(p))
-        if (opts.sample_first < 0) return fail(ctx, RT_ERR_INVALID, "rt_render: sample_first must be >= 0");
-        const int64_t s0 = opts.sample_first, s1 = std::min<int64_t>((int64_t)opts.sample_first + opts.sample_count, ctx->ray_count);
-        for (int p = 0; p < total_passes; p++) {
-            const int64_t lo = std::max<int64_t>(s0, (int64_t)p * pass_spp), hi = std::min<int64_t>(s1, (int64_t)p * pass_spp + spp_of(p));
-            if (hi <= lo) continue;
-            const uint32_t k0 = (uint32_t)(lo - (int64_t)p * pass_spp), m = (uint32_t)(hi - lo);
-            if ((int)m == spp_of(p)) segs.push_back(Segment{p, 0u, (uint32_t)(pixels * (size_t)m), 0u, 0u});
-            else segs.push_back(Segment{p, 0u, (uint32_t)(pixels * (size_t)m), k0, m});
-        }
-    } else if (opts.ray_count > 0) {
-        if (opts.ray_first < 0) return fail(ctx, RT_ERR_INVALID, "rt_render: ray_first must be >= 0");
-        int64_t start = 0;
-        const int64_t u0 = opts.ray_first, u1 = opts.ray_first + opts.ray_count;
-        for (int p = 0; p < total_passes && start < u1; p++) {
-            const int64_t n = (int64_t)pixels * spp_of(p);
-            const int64_t lo = std::max(u0, start), hi = std::min(u1, start + n);
-            if (hi > lo) segs.push_back(Segment{p, (uint32_t)(lo - start), (uint32_t)(hi - lo), 0u, 0u});
-            start += n;
-        }
-    } else {
-        const int pass_first = std::max(0, opts.pass_first);
-        const int pass_end = opts.pass_count > 0 ? std::min(total_passes, pass_first + opts.pass_count) : total_passes;
-        for (int p = pass_first; p < pass_end; p++) segs.push_back(Segment{p, 0u, (uint32_t)(pixels * (size_t)spp_of(p)), 0u, 0u});
-    }
-    auto whole = [&](const Segment &g) { return g.sub_count == 0 && g.offset == 0 && (size_t)g.count == pixels * (size_t)spp_of(g.pass); };
+    auto spp_of = [&](int p) { return shape.spp_of(p); };
+    if (const char *bad = call_segments(shape, opts.pass_first, opts.pass_count, opts.ray_first, opts.ray_count, opts.sample_first, opts.sample_count, segs))
+        return fail(ctx, RT_ERR_INVALID, bad);
     const int n_segs = (int)segs.size();
     const bool collect = opts.collect_stats != 0;
     const bool timing = opts.kernel_timing != 0;  // CUDA-event pair around every bounce kernel and every reorder pass
@@ -1010,91 +983,9 @@ int render_impl(rt_ctx *ctx, const rt_render_opts *opts_in, rt_stats *stats)
     // A WAVE is `group` consecutive passes of equal size traced together: every pass keeps the reference's seeds
     // (they depend on the pass, not on the launch), while the late bounces - a few 10^4 rays per pass, latency-bound -
     // and the launch gaps are paid once per wave instead of once per pass.
-    // Whole passes first, partial passes (the ends of a ray / sample range) after them: a partial pass rides along as the LAST
-    // member of a wave of whole passes with the same samples per pixel (the member index of a ray is id / pass_rays, which needs
-    // full-size members in front). On its own it would be a whole chain of latency-bound launches for a fraction of a pass: a
-    // quarter pass as its own wave cost teapot's 8-GPU share 2 ms of 19 (profiles/r2f_partial.md).
-    // A run of equal passes that needs MORE waves than there are pipes is dealt out evenly (50 passes with room for 16: 13 + 13 + 12
-    // + 12, not 16 + 16 + 16 + 2; wave count a multiple of the pipes where that fits), so that the pipes finish together: teapot
-    // 1000x1000 whole frame 130.3 -> 128.7 ms, lamp 1000x1000 240.4 -> 238.2. A run that fits ONE round of waves keeps the
-    // first-fit plan (6 passes + a partial one on three pipes: (2 + partial) + 3 + 1): there the unequal waves help, because the
-    // short waves' chains of late bounces run while the long wave still has bulk work (teapot's share of 8: 17.09 ms first-fit,
-    // 17.44 ms as 2 + 2 + (2 + partial); profiles/r2g_waves.md).
-    std::stable_partition(segs.begin(), segs.end(), whole);
-    const int n_whole = (int)(std::find_if(segs.begin(), segs.end(), [&](const Segment &g) { return !whole(g); }) - segs.begin());
-    struct WavePlan {
-        Segment member[kMaxPassGroup];
-        int group, partial_member;
-    };
-    std::vector<WavePlan> plan;
-    std::vector<char> rides(n_segs, 0);  // partial passes that found a wave
-    for (int wi = 0; wi < n_whole;) {
-        const int spp0 = spp_of(segs[wi].pass);
-        int run = 0;
-        while (wi + run < n_whole && spp_of(segs[wi + run].pass) == spp0) run++;
-        std::vector<int> riders;  // partial passes that can ride with this run, largest first
-        for (int j = n_whole; j < n_segs; j++)
-            if (!rides[j] && spp_of(segs[j].pass) == spp0 && (size_t)segs[j].count < pixels * (size_t)spp0) riders.push_back(j);
-        std::stable_sort(riders.begin(), riders.end(), [&](int x, int y) { return segs[x].count > segs[y].count; });
-        const int P0 = max_group >= 2 ? std::min<int>((int)riders.size(), run) : 0;
-        if ((run + P0 + max_group - 1) / max_group <= pipes) {
-            // one round: first fit, in queue order; a slot is kept for a rider while one is waiting
-            std::stable_sort(riders.begin(), riders.end());
-            size_t next_rider = 0;
-            for (int left = run; left > 0;) {
-                WavePlan wp{};
-                const int room = std::max(1, max_group - (next_rider < riders.size() ? 1 : 0));
-                while (wp.group < room && left > 0) { wp.member[wp.group++] = segs[wi++]; left--; }
-                wp.partial_member = -1;
-                if (next_rider < riders.size() && wp.group < max_group) {
-                    const int j = riders[next_rider++];
-                    rides[j] = 1;
-                    wp.partial_member = wp.group;
-                    wp.member[wp.group++] = segs[j];
-                }
-                plan.push_back(wp);
-            }
-            continue;
-        }
-        // W waves: wave k holds run / W whole passes (+ 1 for the first run % W waves); the last P waves carry one rider each
-        auto fits = [&](int W, int P) {
-            if (W < 1 || W > run || P > W) return false;
-            for (int k = 0; k < W; k++)
-                if (run / W + (k < run % W ? 1 : 0) + (k >= W - P ? 1 : 0) > max_group) return false;
-            return true;
-        };
-        int W = run, P = 0;
-        for (int p = P0; p >= 0; p--) {  // drop riders that do not fit
-            int first = 0;
-            for (int w = 1; w <= run && !first; w++) if (fits(w, p)) first = w;
-            if (!first) continue;
-            W = first;
-            P = p;
-            const int up = (W + pipes - 1) / pipes * pipes;
-            if (W > 1 && up != W && fits(up, p)) W = up;
-            break;
-        }
-        for (int k = 0; k < W; k++) {
-            WavePlan wp{};
-            const int n = run / W + (k < run % W ? 1 : 0);
-            for (int m = 0; m < n; m++) wp.member[wp.group++] = segs[wi++];
-            wp.partial_member = -1;
-            if (k >= W - P) {  // the last wave (the smallest) takes the largest rider
-                const int j = riders[W - 1 - k];
-                rides[j] = 1;
-                wp.partial_member = wp.group;
-                wp.member[wp.group++] = segs[j];
-            }
-            plan.push_back(wp);
-        }
-    }
-    for (int j = n_whole; j < n_segs; j++)  // partial passes without company: each is a wave of its own
-        if (!rides[j]) {
-            WavePlan wp{};
-            wp.member[wp.group++] = segs[j];
-            wp.partial_member = 0;
-            plan.push_back(wp);
-        }
+    // Which passes go into which wave: plan_waves (wave_plan.cuh; partial passes ride as the last member of a wave of whole passes,
+    // large runs are dealt out in equal waves, one-round calls first fit).
+    const std::vector<WavePlan> plan = plan_waves(segs, shape, max_group, pipes);
     for (const WavePlan &wp : plan) {
         const Segment *member = wp.member;
         const int group = wp.group, partial_member = wp.partial_member;
@@ -1431,6 +1322,33 @@ __global__ void __launch_bounds__(256) probe_copy_kernel(const float4 *__restric
         }
 }
 }  // namespace
+
+extern "C" int rt_plan_waves(const rt_render_opts *opts_in, int width, int height, int ray_count, int max_group, int pipes,
+                             int64_t *out, int64_t out_capacity)
+{
+    if (width <= 0 || height <= 0 || ray_count < 0 || max_group < 1 || max_group > kMaxPassGroup || pipes < 1 || (!out && out_capacity > 0))
+        return RT_ERR_INVALID;
+    rt_render_opts opts{};
+    if (opts_in) opts = *opts_in;
+    const int pass_spp = opts.pass_spp > 0 ? opts.pass_spp : 20;
+    const FrameShape shape{(size_t)width * (size_t)height, ray_count, pass_spp};
+    if (shape.pixels * (size_t)pass_spp >= (1ull << 31)) return RT_ERR_INVALID;
+    std::vector<PassSegment> segs;
+    if (call_segments(shape, opts.pass_first, opts.pass_count, opts.ray_first, opts.ray_count, opts.sample_first, opts.sample_count, segs))
+        return RT_ERR_INVALID;
+    const std::vector<WavePlan> plan = plan_waves(segs, shape, max_group, pipes);
+    int64_t at = 0;
+    for (const WavePlan &wp : plan) {
+        if (at + 2 + 5 * (int64_t)wp.group > out_capacity) return RT_ERR_INVALID;
+        out[at++] = wp.group;
+        out[at++] = wp.partial_member;
+        for (int m = 0; m < wp.group; m++) {
+            const PassSegment &g = wp.member[m];
+            out[at++] = g.pass; out[at++] = g.offset; out[at++] = g.count; out[at++] = g.sub_first; out[at++] = g.sub_count;
+        }
+    }
+    return (int)plan.size();
+}
 
 extern "C" int rt_probe_copy_gbs(rt_ctx *ctx, int64_t bytes, int32_t iters, double *out_gbs)
 {

@@ -227,6 +227,15 @@ int rt_sort_pairs_static(rt_ctx *ctx, const uint32_t *d_keys_in, const uint32_t 
  * CUDA events. With a buffer pair that fits the L2 it gives the L2 bandwidth bench.py's roofline.l2_frac is quoted against;
  * with a large one, the HBM copy bandwidth (the figure MEASURED_PEAKS.json holds). */
 int rt_probe_copy_gbs(rt_ctx *ctx, int64_t bytes, int32_t iters, double *out_gbs);
+/* Test hook (host only: no context, no device): the planning half of rt_render — which rays of which passes a call with these
+ * options traces (its segments: whole passes, or the pieces a sample_* / ray_* / pass_* range cuts out of them) and how they
+ * are grouped into waves of at most max_group (1..16) passes on `pipes` streams — for a frame of width x height pixels with
+ * ray_count samples per pixel. No counterpart in the reference (its loop is one pass at a time, raytracing.cu:222-247).
+ * Writes per wave {members, partial_member (-1: none; else the index of the wave's partial pass, always its last member or
+ * its only one), then per member: pass, offset, count, sub_first, sub_count} as int64 values; returns the number of waves
+ * (>= 0) or RT_ERR_INVALID (option out of range, out_capacity too small). */
+int rt_plan_waves(const rt_render_opts *opts, int width, int height, int ray_count, int max_group, int pipes, int64_t *out,
+                  int64_t out_capacity);
 /* Host mirror of the kernels' index arithmetic (ray id -> pass / pixel / row: n / d by multiply-and-shift with the constants
  * the render call derives from d). Needs no device; d = 0 is treated as 1. Test hook. */
 uint32_t rt_index_divide(uint32_t n, uint32_t d);

@@ -360,5 +360,10 @@ python -c "from cuda_raytracer_b200.core import kernel_id, build_id; print(kerne
 timeout 200 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-ref-gpu --no-extras > gpurun_out/c31_bench.json 2> gpurun_out/c31_bench.err
 echo "bench rc=$?" >> gpurun_out/c31_bench.err
 ;;
-*) echo "usage: $0 <call>: 01 02 03 03s 04 05 06 07 08 09 10 11 12 13 14 15 16 17 18 19 20 21 22 23 24 25 26 27 28 29 30 31"; exit 2 ;;
+32)  # planner moved into wave_plan.cuh behind rt_plan_waves (host-only refactor): whole GPU suite + teapot's share of 8
+timeout 300 python -m pytest tests -q -m gpu -x > gpurun_out/c32_tests.log 2>&1
+echo "tests rc=$?" >> gpurun_out/c32_tests.log
+timeout 60 python tools/share_probe.py teapot 1000 1000 1000 10 8 0 2>&1 | grep -E "whole|auto" > gpurun_out/c32_share.log
+;;
+*) echo "usage: $0 <call>: 01 02 03 03s 04 05 06 07 08 09 10 11 12 13 14 15 16 17 18 19 20 21 22 23 24 25 26 27 28 29 30 31 32"; exit 2 ;;
 esac
