@@ -222,7 +222,7 @@ def reference_arm(args, rank, world, emit):
 
 
 # ---- the B200 arm ------------------------------------------------------------------------------------------------------
-def agreeing_runs(measure, least=3, most=7, tol=0.02):
+def agreeing_runs(measure, least=3, most=5, tol=0.02):
     """Samples of a timer with one-sided noise: at least `least`, then more until the two smallest agree to `tol` (or `most` runs).
     The smallest is the estimate; a single lucky-looking outlier downwards does not exist for such a timer."""
     runs, tries = [], 0
@@ -293,7 +293,7 @@ def ref_gpu_timing(scene, w, h, bounces, lpp):
         m = re.search(r"GPU Took ([0-9.eE+-]+)s", o)
         return float(m.group(1)) if m else None
 
-    out = {"config": f"{scene}.scene {w}x{h}, `GPU Took` at {list(pts)} spp, per point the smallest of 3-7 runs (until the two smallest agree to 2 %), least-squares slope = steady state"}
+    out = {"config": f"{scene}.scene {w}x{h}, `GPU Took` at {list(pts)} spp, per point the smallest of 3-5 runs (until the two smallest agree to 2 %), least-squares slope = steady state"}
     try:
         for flags in ((), ("no_sort",)):
             mode = "no_sort" if flags else "sort"
