@@ -144,6 +144,27 @@ static inline int ray_aabb(const float *mn, const float *mx, v3 o, v3 n_inv, flo
     return tmin <= tmax;
 }
 
+/* DIAGNOSTIC ONLY (near_first == 2 in the closest-hit entry points; tools/slow_ray_study.py): the slab test in the form the CUDA
+ * core evaluates it (traverse.cuh: box as centre + half-extent rounded up, t_centre = fma(c, 1/d, -(o * 1/d)), t_near / t_far =
+ * fma(-+h, |1/d|, t_centre), NaN = no constraint) — to count the records THAT form visits for a given ray. Not pinned to any
+ * reference vector: it restates the product, not the reference. */
+static inline int ray_aabb_device_form(const float *mn, const float *mx, v3 o, v3 n_inv, float *tmin_out, float tmax)
+{
+    float c[3], h[3];
+    for (int k = 0; k < 3; k++) {
+        c[k] = 0.5f * (mn[k] + mx[k]);
+        float hk = fmaxf(mx[k] - c[k], c[k] - mn[k]);
+        h[k] = nextafterf(hk, INFINITY);
+    }
+    const float sox = -(o.x * n_inv.x), soy = -(o.y * n_inv.y), soz = -(o.z * n_inv.z);
+    const float ax = fabsf(n_inv.x), ay = fabsf(n_inv.y), az = fabsf(n_inv.z);
+    const float tx = fmaf(c[0], n_inv.x, sox), ty = fmaf(c[1], n_inv.y, soy), tz = fmaf(c[2], n_inv.z, soz);
+    const float tn = fmaxf(fmaxf(fmaf(-h[0], ax, tx), fmaf(-h[1], ay, ty)), fmaxf(fmaf(-h[2], az, tz), 0.0f));
+    const float tf = fminf(fminf(fmaf(h[0], ax, tx), fmaf(h[1], ay, ty)), fminf(fmaf(h[2], az, tz), tmax));
+    *tmin_out = tn;
+    return tn <= tf;
+}
+
 int oracle_ray_aabb(const float *aabb6, const float *ray6, float tmax, float *tmin_out)
 {
     v3 d = ld3(ray6 + 3);
@@ -196,8 +217,14 @@ static void bvh_closest_hit(const oracle_scene *s, v3 o, v3 d, int near_first, f
             if (c) c->internal_visits++;
             float d1, d2;
             const oracle_node *n1 = &s->bvh[node->child1], *n2 = &s->bvh[node->child2];
-            int hit1 = ray_aabb(n1->min_bound, n1->max_bound, o, n_inv, &d1, *closest);
-            int hit2 = ray_aabb(n2->min_bound, n2->max_bound, o, n_inv, &d2, *closest);
+            int hit1, hit2;
+            if (near_first == 2) {
+                hit1 = ray_aabb_device_form(n1->min_bound, n1->max_bound, o, n_inv, &d1, *closest);
+                hit2 = ray_aabb_device_form(n2->min_bound, n2->max_bound, o, n_inv, &d2, *closest);
+            } else {
+                hit1 = ray_aabb(n1->min_bound, n1->max_bound, o, n_inv, &d1, *closest);
+                hit2 = ray_aabb(n2->min_bound, n2->max_bound, o, n_inv, &d2, *closest);
+            }
             if (hit1 && hit2) {
                 /* reference: nearer child pushed first => popped last (Q5) */
                 int first_is_1 = d1 < d2;

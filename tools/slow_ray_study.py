@@ -2,7 +2,7 @@
 records per closest-hit query, bounce by bounce — the rays that set the duration of a late-bounce trace launch on the GPU
 (profiles/r2g_waves.md: one launch of lamp 1000x1000's pass 23 lasts 2.1 ms instead of 0.33).
 
-usage: slow_ray_study.py <scene> <w> <h> <spp> <bounces> <pass> [first_bounce_to_examine]
+usage: slow_ray_study.py <scene> <w> <h> <spp> <bounces> <pass> [first_bounce_to_examine [walk_form 1|2]]
 The pass is stepped with the oracle under the GPU path's seeds (ray index x 4137874753 + 279220567 x (remaining x 20 + bounce),
 raytracing.cu:89,229,236); before every step from `first_bounce` on, the live rays are walked once more in chunks of 256 with
 the visit counters on (near-child-first order, as the CUDA core walks), the heaviest chunks are resolved ray by ray."""
@@ -21,6 +21,7 @@ from util import load, oracle_arrays  # noqa: E402
 name = sys.argv[1]
 w, h, spp, bounces, pass_index = (int(v) for v in sys.argv[2:7])
 first_bounce = int(sys.argv[7]) if len(sys.argv) > 7 else 2
+walk_form = int(sys.argv[8]) if len(sys.argv) > 8 else 1  # 1 = the reference's slab test (near child first), 2 = the CUDA core's form
 A = oracle_arrays(load(name).set_image(w, h, spp, bounces, 1.0))
 S = A.oracle_struct()
 L = po.port()
@@ -36,7 +37,7 @@ def visits(rays6):
     c = po.Counters()
     m = len(rays6)
     t, idx = np.zeros(m, np.float32), np.zeros(m, np.int32)
-    L.oracle_closest_hit_ex(C.byref(S), np.ascontiguousarray(rays6), m, 1, 1, t, idx, C.byref(c))
+    L.oracle_closest_hit_ex(C.byref(S), np.ascontiguousarray(rays6), m, walk_form, 1, t, idx, C.byref(c))
     return c.internal_visits, c.triangle_tests
 
 
